@@ -1,0 +1,141 @@
+/*
+ * mg_b200.h -- C ABI of libmagical_b200.so, the B200-native batched MAGICAL simulator.
+ *
+ * This is the drop-in boundary for the per-step hot path of khanhptnk/magical-1.
+ * The reference has no FFI of its own (it is pure Python over pymunk/pygame/cv2), so
+ * each entry point below names the reference Python interface it stands in for
+ * (paths relative to /root/reference):
+ *
+ *   mg_create / mg_destroy    BaseEnv.__init__ / close              magical/base_env.py:78-123, 353-356
+ *                             + lores_*_entry_point wrapper stack    magical/benchmarks/__init__.py:232-266
+ *   mg_set_scenes             BaseEnv.reset (space + entities built  magical/base_env.py:190-246
+ *                             from host-sampled on_reset() results)  magical/benchmarks/<task>.py on_reset
+ *   mg_step / mg_step_host    BaseEnv.step                           magical/base_env.py:267-307
+ *                               Robot.set_action / Robot.update      magical/entities.py:435-476
+ *                               pm.Space.step x10                    magical/base_env.py:248-255
+ *                               score_on_end_of_traj                 magical/benchmarks/<task>.py
+ *                               render('rgb_array') ego/allo         magical/base_env.py:324-343, magical/render.py:385-395
+ *                               ResizeDictObservation (INTER_AREA)   magical/benchmarks/__init__.py:150-190
+ *                               FlattenFrameStack/EagerDictFrameStack magical/benchmarks/__init__.py:51-147
+ *   mg_render                 BaseEnv.render(mode='rgb_array')       magical/base_env.py:324-343
+ *   mg_score                  score_on_end_of_traj()                 magical/benchmarks/*.py
+ *   mg_debug_reward           debug_shaped_reward()                  move_to_corner.py:86-100, pick_and_place.py:114-124
+ *   mg_get_bodies             body.position/.angle/.velocity reads   magical/base_env.py:358-413 (debug_print_entity_spec)
+ *   mg_get_state/mg_set_state (no reference equivalent: EzPickle re-constructs, base_env.py:20-46)
+ *   mg_host_entity_overlaps   space.shape_query in the placement     magical/geom.py:226-233
+ *                             sampler (host-side reset only)
+ *
+ * Conventions: plain pointers and sizes; no exceptions cross the boundary; every call
+ * returns 0 on success or a negative MG_ERR_* code and records a message readable with
+ * mg_last_error(); `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ * pointers named *_dev are device pointers owned by the caller, *_host are host pointers.
+ * One handle per GPU; calls on one handle must be serialised by the caller.
+ * There is NO CPU implementation behind this ABI: mg_create fails if no CUDA device is
+ * usable.
+ */
+#ifndef MG_B200_H
+#define MG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "mg_scene.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MG_OK 0
+#define MG_ERR_ARG (-1)
+#define MG_ERR_CUDA (-2)
+#define MG_ERR_NODEVICE (-3)
+
+#define MG_VIEW_ALLO 0
+#define MG_VIEW_EGO 1
+#define MG_MAX_GROUPS 8          /* 3-channel groups in a stacked observation (8 = LoResStack allo4+ego4) */
+#define MG_MAX_BODIES 16         /* robot group (6) + MG_MAX_BLOCKS */
+
+typedef struct mg_handle mg_handle;
+
+/* Observation layout produced by mg_step: `n_groups` RGB groups concatenated on the
+ * channel axis, group g = the frame of view group_view[g] that is group_age[g] steps old
+ * (0 = newest).  LoRes4E: 4 groups, view EGO, ages 3,2,1,0 (oldest first,
+ * benchmarks/__init__.py:122-129). */
+typedef struct mg_config {
+    int32_t device;               /* CUDA ordinal */
+    int32_t num_envs;
+    int32_t n_groups;
+    int32_t group_view[MG_MAX_GROUPS];
+    int32_t group_age[MG_MAX_GROUPS];
+    int32_t chw;                  /* 1: obs is [B, 3*n_groups, 96, 96] (ChannelsFirst, :193-216); 0: [B,96,96,3*n_groups] */
+    int32_t reserved[5];
+} mg_config;
+
+int mg_create(const mg_config *cfg, mg_handle **out);
+int mg_destroy(mg_handle *h);
+const char *mg_last_error(const mg_handle *h); /* h may be NULL: error of the last failed mg_create */
+
+/* Reset `n` envs to host-sampled scenes.  env_ids_host == NULL means envs 0..n-1.
+ * The frame stacks of those envs are refilled with the first rendered frame on the next
+ * mg_step / mg_reset_obs (FlattenFrameStack.reset, benchmarks/__init__.py:139-147). */
+int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream);
+
+/* Render the current state of every env into the frame stacks and write the stacked
+ * observation (what reset() returns).  obs_dev: u8 [B,96,96,3*n_groups] (or CHW). */
+int mg_reset_obs(mg_handle *h, uint8_t *obs_dev, void *stream);
+
+/* One env-step for all envs: action decode, 10 physics sub-steps, horizon/score, render,
+ * 4x area downsample, frame stack.  reward/done/score may be NULL.
+ * score_dev receives info['eval_score'] (0 until the last step of the episode). */
+int mg_step(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev,
+            uint8_t *done_dev, float *score_dev, void *stream);
+
+/* Physics + score only (no render); used by mg_step and by callers that reset done envs
+ * between the physics and the render of a step.  */
+int mg_step_physics(mg_handle *h, const int32_t *actions_dev, float *reward_dev, uint8_t *done_dev,
+                    float *score_dev, void *stream);
+int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream);
+
+/* Same as mg_step with HOST buffers: H2D of actions, D2H of obs/reward/done/score and a
+ * stream synchronise are inside the call (the end-to-end path). */
+int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *obs_host, float *reward_host,
+                 uint8_t *done_host, float *score_host);
+
+/* Render one view of every env.  full_res != 0: out_dev u8 [B,384,384,3];
+ * else the 4x area-averaged u8 [B,96,96,3].  Does not touch the frame stacks. */
+int mg_render(mg_handle *h, int view, int full_res, uint8_t *out_dev, void *stream);
+
+int mg_score(mg_handle *h, float *score_dev, void *stream);
+int mg_debug_reward(mg_handle *h, float *reward_dev, void *stream);
+
+/* Body poses/velocities, canonical order: the six robot bodies (MG_RB_*), then blocks in
+ * scene order; unused slots are zero.  out_host: double [B][MG_MAX_BODIES][6] = x,y,angle,vx,vy,w.
+ * Synchronous. */
+int mg_get_bodies(mg_handle *h, double *out_host);
+
+/* Opaque per-env checkpoint blobs (bodies, cached impulses, contact cache, counters). */
+size_t mg_state_size(const mg_handle *h);
+int mg_get_state(mg_handle *h, const int32_t *env_ids_host, int n, void *blobs_host);
+int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, const void *blobs_host);
+
+/* Kernel launches issued through this handle so far (for bench.py's gpu_launches). */
+int64_t mg_launch_count(const mg_handle *h);
+/* CUDA-event time (ms) accumulated over the physics / render kernels since the last call
+ * with reset != 0; which: 0 physics, 1 render.  Only counted while mg_set_timing(h,1). */
+int mg_set_timing(mg_handle *h, int enable);
+double mg_kernel_ms(mg_handle *h, int which, int reset, int64_t *launches_out);
+
+/* ---- host-side helpers for reset sampling (no GPU involved) ---- */
+
+enum { MG_ENT_ROBOT = 0, MG_ENT_BLOCK = 1, MG_ENT_GOAL = 2 };
+
+/* 1 if entity (kind, idx) of `scene`, at the pose the scene holds for it, touches an arena
+ * wall or any shape of the entities selected by the masks (bit i = block i / goal i;
+ * robot_active != 0 = robot).  Stands in for the shape_query loop of
+ * geom.pm_randomise_pose (geom.py:226-233); touching counts (distance <= 0). */
+int mg_host_entity_overlaps(const mg_scene *scene, int kind, int idx, int robot_active,
+                            uint32_t block_mask, uint32_t goal_mask);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MG_B200_H */

@@ -1,0 +1,46 @@
+/*
+ * mg_kernels.h -- device-side handle and kernel launchers shared by mg_api.cu,
+ * mg_physics.cu and mg_raster.cu.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include "mg_state.cuh"
+#include "../../include/mg_b200.h"
+
+#define MG_MAX_RING 4   /* frames kept per view (deepest reference stack: 4, benchmarks/__init__.py:232-306) */
+#define MG_FRAME_BYTES (MG_LORES * MG_LORES * 3)
+
+struct MgDeviceState {
+    int num_envs;
+    double *dstate;          /* [groups][D_NF][32] */
+    int *istate;             /* [groups][I_NF][32] */
+    mg_scene *scenes;        /* [B] scene each env was last reset to */
+    MgPrim *prims;           /* [B][MG_MAX_PRIMS] draw list */
+    int *n_prims;            /* [B] */
+    double *poses;           /* [B][MG_NB][MG_POSE_NF] exported after every reset / step */
+    const MgTables *tables;  /* device copy */
+    /* frame stacks: ring[view] = u8 [B][MG_MAX_RING][96][96][3]; head[env] = slot of the newest frame */
+    uint8_t *ring[2];
+    int *ring_head;          /* [B][2] */
+};
+
+struct MgObsSpec {
+    int n_groups;
+    int view[MG_MAX_GROUPS];
+    int age[MG_MAX_GROUPS];
+    int chw;
+    int render_view[2];      /* which views mg_step must render */
+};
+
+void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st);
+void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st);
+void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);
+/* render `view` of every env into the frame stacks (push) */
+void mg_launch_render_push(const MgDeviceState &S, int view, cudaStream_t st);
+/* compose the stacked observation from the rings */
+void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, uint8_t *obs, cudaStream_t st);
+/* clear the per-env "fresh" flag after all views were pushed */
+void mg_launch_clear_fresh(const MgDeviceState &S, cudaStream_t st);
+/* stand-alone render of one view: full_res ? [B,384,384,3] : [B,96,96,3] */
+void mg_launch_render_out(const MgDeviceState &S, int view, int full_res, uint8_t *out, cudaStream_t st);
+void mg_launch_state_gather(const MgDeviceState &S, const int32_t *env_ids_dev, int n, double *dblobs, int *iblobs, int scatter, cudaStream_t st);

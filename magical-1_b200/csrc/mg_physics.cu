@@ -1,0 +1,1034 @@
+/*
+ * mg_physics.cu -- reset expansion, the per-step rigid-body kernel and the score kernels.
+ *
+ * One thread owns one env (one pymunk Space of the reference) and runs, in Chipmunk's
+ * order, everything BaseEnv.step does before rendering (magical/base_env.py:267-292):
+ *   Robot.set_action                      magical/entities.py:435-453
+ *   10 x ( Robot.update ; Space.step )    magical/base_env.py:248-255, magical/entities.py:455-476
+ *   episode counter / done / score        magical/base_env.py:284-292
+ * Space.step is Chipmunk2D 7.0.3's cpSpaceStep as configured by base_env.py:206-208
+ * (iterations 10, collision_slop 0.01, no gravity, damping 1): position integration,
+ * narrow phase over all shape pairs in add order, arbiter cache with warm starting,
+ * pre-step, cached impulses, 10 sequential-impulse iterations over arbiters then
+ * constraints in add order.  All arithmetic is IEEE double without FMA contraction.
+ *
+ * Lanes of a warp are 32 different envs; state is field-major per 32-env group
+ * (mg_state.cuh), so every state access of a warp is one 256-byte row.
+ */
+#include <cuda_runtime.h>
+#include "mg_state.cuh"
+#include "mg_kernels.h"
+
+struct EnvRef { double *d; int *i; };
+#define DF(e, f) ((e).d[(size_t)(f) * MG_GROUP])
+#define IF(e, f) ((e).i[(size_t)(f) * MG_GROUP])
+#define BF(e, b, f) DF(e, D_BODY0 + (b) * B_NF + (f))
+#define CF(e, c, f) DF(e, D_CON0 + (c) * C_NF + (f))
+#define AF(e, a, f) DF(e, D_ARB0 + (a) * A_NF + (f))
+#define ACF(e, a, k, f) DF(e, D_ARB0 + (a) * A_NF + A_CON0 + (k) * AC_NF + (f))
+#define AIF(e, a, f) IF(e, I_ARB0 + (a) * 4 + (f))
+
+__device__ __forceinline__ EnvRef env_ref(double *dstate, int *istate, int env)
+{
+    EnvRef e;
+    e.d = dstate + mg_field_index(env, D_NF, 0);
+    e.i = istate + mg_field_index(env, I_NF, 0);
+    return e;
+}
+
+#define MG_DT ((1.0 / 8) / 10)   /* fps = 8 (benchmarks/__init__.py:435), phys_steps = 10 (base_env.py:249) */
+
+/* ------------------------------------------------------------------ reset expansion */
+
+__device__ void init_body(EnvRef e, int b, int dynamic, double m, double i, double x, double y, double a)
+{
+    for (int f = 0; f < B_NF; f++) BF(e, b, f) = 0.0;
+    BF(e, b, B_PX) = x; BF(e, b, B_PY) = y; BF(e, b, B_A) = a;
+    double s, c;
+    sincos(a, &s, &c);
+    BF(e, b, B_RX) = c; BF(e, b, B_RY) = s;
+    BF(e, b, B_MINV) = dynamic ? 1.0 / m : 0.0;
+    BF(e, b, B_IINV) = dynamic ? 1.0 / i : 0.0;
+}
+
+__device__ int add_con(EnvRef e, int kind, int a, int b, double max_force, double max_bias, double bc)
+{
+    int c = IF(e, I_NCON);
+    IF(e, I_NCON) = c + 1;
+    IF(e, I_CON0 + c) = kind | (a << 8) | (b << 16);
+    for (int f = 0; f < C_NF; f++) CF(e, c, f) = 0.0;
+    CF(e, c, C_JMAX) = max_force * MG_DT;
+    CF(e, c, C_MAXBIAS) = max_bias;
+    CF(e, c, C_BC) = bc;
+    return c;
+}
+
+__device__ void add_shape(EnvRef e, int tpl, int body, int ent)
+{
+    int s = IF(e, I_NSHAPES);
+    IF(e, I_NSHAPES) = s + 1;
+    IF(e, I_SHAPE0 + s) = tpl | (body << 8) | (ent << 16);
+}
+
+__device__ void add_prim(MgPrim *prims, int *n, int dl, int chain, int body, int fill, int outline, int mode, int aux)
+{
+    MgPrim p;
+    p.dl = (uint8_t)dl; p.chain = (uint8_t)chain; p.body = (uint8_t)body; p.fill = (uint8_t)fill;
+    p.outline = (uint8_t)outline; p.mode = (uint8_t)mode; p.aux = (uint8_t)aux; p.pad = 0;
+    prims[(*n)++] = p;
+}
+
+/* Robot.setup (entities.py:238-433) */
+__device__ void setup_robot(EnvRef e, const MgTables *T, const mg_scene *sc, MgPrim *prims, int *np)
+{
+    const double radius = 0.2, mass = 1.0, inf = INFINITY;
+    const int rb = MG_BODY_ROBOT;
+    double inertia = mass * (0.5 * (0.0 * 0.0 + radius * radius) + 0.0);
+    init_body(e, rb + MG_RB_ROBOT, 1, mass, inertia, sc->robot[MG_RB_ROBOT][0], sc->robot[MG_RB_ROBOT][1], sc->robot[MG_RB_ROBOT][2]);
+    init_body(e, rb + MG_RB_CONTROL, 0, 0, 0, sc->robot[MG_RB_CONTROL][0], sc->robot[MG_RB_CONTROL][1], sc->robot[MG_RB_CONTROL][2]);
+    add_con(e, CON_PIVOT, rb + MG_RB_CONTROL, rb + MG_RB_ROBOT, sc->phys[0], 0.0, T->bias_coef_default);
+    int c = add_con(e, CON_GEAR, rb + MG_RB_CONTROL, rb + MG_RB_ROBOT, sc->phys[1], 2.5, 1.0);
+    CF(e, c, C_P0) = 0.0; CF(e, c, C_P1) = 1.0;
+    for (int k = 0; k < 2; k++) {
+        double eye_mass = mass / 10;
+        double eye_inertia = eye_mass * (0.5 * (radius * radius));
+        int pb = rb + MG_RB_PUPIL_L + k;
+        init_body(e, pb, 1, eye_mass, eye_inertia, sc->robot[MG_RB_PUPIL_L + k][0], sc->robot[MG_RB_PUPIL_L + k][1], sc->robot[MG_RB_PUPIL_L + k][2]);
+        c = add_con(e, CON_SPRING, rb + MG_RB_ROBOT, pb, 0.001, 3.0, T->bias_coef_default);
+        CF(e, c, C_P0) = T->spring_w_coef;
+    }
+    for (int k = 0; k < 2; k++) {
+        double side = k == 0 ? -1.0 : 1.0;
+        double lower = k == 0 ? -0.0 : -(M_PI / 8);
+        double upper = k == 0 ? (M_PI / 8) : 0.0;
+        int fb = rb + MG_RB_FINGER_L + k;
+        init_body(e, fb, 1, mass / 8, T->finger_moment[k], sc->robot[MG_RB_FINGER_L + k][0], sc->robot[MG_RB_FINGER_L + k][1], sc->robot[MG_RB_FINGER_L + k][2]);
+        c = add_con(e, CON_PIVOT, rb + MG_RB_ROBOT, fb, inf, inf, 1.0);
+        CF(e, c, C_P0) = side * radius * 0.45; CF(e, c, C_P1) = radius * 0.1;
+        c = add_con(e, CON_LIMIT, rb + MG_RB_ROBOT, fb, inf, inf, 1.0);
+        CF(e, c, C_P0) = lower; CF(e, c, C_P1) = upper;
+        c = add_con(e, CON_MOTOR, rb + MG_RB_ROBOT, fb, sc->phys[2], 0.0, T->bias_coef_default);
+        CF(e, c, C_P0) = 0.0;
+    }
+    add_shape(e, MG_TPL_CIRCLE_ROBOT, rb + MG_RB_ROBOT, MG_ENTID_ROBOT);
+    for (int k = 0; k < 2; k++)
+        for (int part = 0; part < 2; part++)
+            add_shape(e, MG_TPL_FINGER0 + k * 2 + part, rb + MG_RB_FINGER_L + k, MG_ENTID_ROBOT);
+    /* graphics, entities.py:374-433 */
+    for (int k = 0; k < 2; k++)
+        for (int part = 0; part < 2; part++)
+            add_prim(prims, np, MG_DL_FINGER_OUT0 + k * 2 + part, MG_CHAIN_BODY, rb + MG_RB_FINGER_L + k, MG_PAL_GREY, 0, 0, 0);
+    for (int k = 0; k < 2; k++)
+        for (int part = 0; part < 2; part++)
+            add_prim(prims, np, MG_DL_FINGER_IN0 + k * 2 + part, MG_CHAIN_BODY, rb + MG_RB_FINGER_L + k, MG_PAL_GREY_LIGHT, 0, 0, 0);
+    add_prim(prims, np, MG_DL_ROBOT, MG_CHAIN_BODY, rb + MG_RB_ROBOT, MG_PAL_GREY, MG_PAL_GREY_DARK, 1, 0);
+    for (int k = 0; k < 2; k++) {
+        add_prim(prims, np, MG_DL_EYE, MG_CHAIN_EYE, rb + MG_RB_ROBOT, MG_PAL_WHITE, 0, 0, k);
+        add_prim(prims, np, MG_DL_PUPIL, MG_CHAIN_PUPIL, rb + MG_RB_PUPIL_L + k, MG_PAL_PUPIL, 0, 0, k);
+    }
+}
+
+/* Shape.setup (entities.py:610-749) */
+__device__ void setup_block(EnvRef e, const MgTables *T, const mg_scene *sc, int bi, MgPrim *prims, int *np)
+{
+    const mg_block *bl = &sc->blocks[bi];
+    const double mass = 0.5, shape_size = 0.2 * 0.6;
+    int body = MG_BODY_BLOCK0 + bi, ent = MG_ENTID_BLOCK0 + bi;
+    int col = MG_PAL_COLOUR0 + bl->colour, dark = MG_PAL_DARK0 + bl->colour;
+    switch (bl->type) {
+    case MG_SQUARE:
+        init_body(e, body, 1, mass, T->square_moment, bl->x, bl->y, bl->angle);
+        add_shape(e, MG_TPL_SQUARE, body, ent);
+        break;
+    case MG_CIRCLE:
+        init_body(e, body, 1, mass, mass * (0.5 * (shape_size * shape_size)), bl->x, bl->y, bl->angle);
+        add_shape(e, MG_TPL_CIRCLE_BLOCK, body, ent);
+        break;
+    case MG_STAR:
+        init_body(e, body, 1, mass, T->star_moment, bl->x, bl->y, bl->angle);
+        for (int k = 0; k < MG_STAR_PIECES; k++) add_shape(e, MG_TPL_STAR0 + k, body, ent);
+        break;
+    default:
+        init_body(e, body, 1, mass, T->pent_moment, bl->x, bl->y, bl->angle);
+        add_shape(e, MG_TPL_PENT, body, ent);
+        break;
+    }
+    /* floor friction: entities.py:700-708 */
+    add_con(e, CON_PIVOT, 0, body, sc->phys[3], 0.0, T->bias_coef_default);
+    int c = add_con(e, CON_GEAR, 0, body, sc->phys[4], 0.0, T->bias_coef_default);
+    CF(e, c, C_P0) = 0.0; CF(e, c, C_P1) = 1.0;
+    switch (bl->type) {
+    case MG_SQUARE: add_prim(prims, np, MG_DL_SQUARE, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
+    case MG_CIRCLE: add_prim(prims, np, MG_DL_CIRCLE, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
+    case MG_STAR:
+        for (int k = 0; k < MG_STAR_PIECES; k++) add_prim(prims, np, MG_DL_STAR_OUT0 + k, MG_CHAIN_BODY, body, dark, 0, 0, 0);
+        for (int k = 0; k < MG_STAR_PIECES; k++) add_prim(prims, np, MG_DL_STAR_IN0 + k, MG_CHAIN_BODY, body, col, 0, 0, 0);
+        break;
+    default: add_prim(prims, np, MG_DL_PENT, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
+    }
+}
+
+__device__ void export_poses(EnvRef e, double *pose)
+{
+    int nb = IF(e, I_NBODIES);
+    for (int b = 0; b < MG_NB; b++) {
+        double *o = pose + b * MG_POSE_NF;
+        if (b < nb) {
+            o[0] = BF(e, b, B_PX); o[1] = BF(e, b, B_PY); o[2] = BF(e, b, B_A);
+            o[3] = BF(e, b, B_VX); o[4] = BF(e, b, B_VY); o[5] = BF(e, b, B_W);
+            o[6] = BF(e, b, B_RX); o[7] = BF(e, b, B_RY);
+        } else {
+            for (int k = 0; k < MG_POSE_NF; k++) o[k] = 0.0;
+        }
+    }
+}
+
+/* BaseEnv.reset after on_reset(): expand host-sampled scenes into simulation state
+ * (magical/base_env.py:190-246; add order arena, goals, [robot], blocks, [robot]). */
+__global__ void mg_init_kernel(MgDeviceState S, const mg_scene *scenes, const int32_t *env_ids, int n)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int env = env_ids ? env_ids[k] : k;
+    const mg_scene *sc = &scenes[k];
+    const MgTables *T = S.tables;
+    EnvRef e = env_ref(S.dstate, S.istate, env);
+    S.scenes[env] = *sc;
+    for (int f = 0; f < I_ARB0; f++) IF(e, f) = 0;
+    IF(e, I_TASK) = sc->task; IF(e, I_HORIZON) = sc->horizon;
+    IF(e, I_NBLOCKS) = sc->n_blocks; IF(e, I_NGOALS) = sc->n_goals;
+    IF(e, I_ROBOT_FIRST) = sc->robot_first; IF(e, I_DEBUG_REWARD) = sc->debug_reward;
+    IF(e, I_TARGET_BLOCK) = sc->target_block; IF(e, I_NVALID) = sc->n_valid_targets;
+    IF(e, I_NBODIES) = 1 + MG_RB_COUNT + sc->n_blocks;
+    IF(e, I_FRESH) = 1;
+    DF(e, D_TARGET) = sc->target_pos[0]; DF(e, D_TARGET + 1) = sc->target_pos[1];
+    init_body(e, 0, 0, 0, 0, 0.0, 0.0, 0.0);
+    MgPrim *prims = S.prims + (size_t)env * MG_MAX_PRIMS;
+    int np = 0;
+    for (int w = 0; w < 4; w++) add_shape(e, MG_TPL_WALL0 + w, 0, MG_ENTID_ARENA);
+    add_prim(prims, &np, MG_DL_ARENA, MG_CHAIN_CAM, 0, MG_PAL_WHITE, MG_PAL_GREY, 1, 0);
+    for (int g = 0; g < sc->n_goals; g++) {
+        const mg_goal *go = &sc->goals[g];
+        DF(e, D_GOAL0 + g * 4 + 0) = go->cx; DF(e, D_GOAL0 + g * 4 + 1) = go->cy;
+        DF(e, D_GOAL0 + g * 4 + 2) = go->h;  DF(e, D_GOAL0 + g * 4 + 3) = go->w;
+        IF(e, I_GOAL0 + g) = go->colour | ((go->want_block + 1) << 8);
+        add_prim(prims, &np, MG_DL_GOAL, MG_CHAIN_GOAL, 0, MG_PAL_LIGHT0 + go->colour, MG_PAL_COLOUR0 + go->colour, 2, g);
+    }
+    for (int b = 0; b < sc->n_blocks; b++)
+        IF(e, I_BLOCK0 + b) = sc->blocks[b].type | (sc->blocks[b].colour << 8) | (sc->blocks[b].role << 16);
+    if (sc->robot_first) setup_robot(e, T, sc, prims, &np);
+    for (int b = 0; b < sc->n_blocks; b++) setup_block(e, T, sc, b, prims, &np);
+    if (!sc->robot_first) setup_robot(e, T, sc, prims, &np);
+    S.n_prims[env] = np;
+    export_poses(e, S.poses + (size_t)env * MG_POSE_STRIDE);
+}
+
+/* ------------------------------------------------------------------ body helpers (chipmunk_private.h) */
+
+__device__ __forceinline__ vec2 body_p(EnvRef e, int b) { return V(BF(e, b, B_PX), BF(e, b, B_PY)); }
+__device__ __forceinline__ vec2 body_v(EnvRef e, int b) { return V(BF(e, b, B_VX), BF(e, b, B_VY)); }
+__device__ __forceinline__ vec2 body_rot(EnvRef e, int b) { return V(BF(e, b, B_RX), BF(e, b, B_RY)); }
+
+__device__ __forceinline__ vec2 relative_velocity(EnvRef e, int a, int b, vec2 r1, vec2 r2)
+{
+    vec2 v1 = vadd(body_v(e, a), vmul(vperp(r1), BF(e, a, B_W)));
+    vec2 v2 = vadd(body_v(e, b), vmul(vperp(r2), BF(e, b, B_W)));
+    return vsub(v2, v1);
+}
+__device__ __forceinline__ void apply_impulse(EnvRef e, int b, vec2 j, vec2 r)
+{
+    double minv = BF(e, b, B_MINV), iinv = BF(e, b, B_IINV);
+    BF(e, b, B_VX) = BF(e, b, B_VX) + j.x * minv;
+    BF(e, b, B_VY) = BF(e, b, B_VY) + j.y * minv;
+    BF(e, b, B_W) = BF(e, b, B_W) + iinv * vcross(r, j);
+}
+__device__ __forceinline__ void apply_impulses(EnvRef e, int a, int b, vec2 r1, vec2 r2, vec2 j)
+{
+    apply_impulse(e, a, vneg(j), r1);
+    apply_impulse(e, b, j, r2);
+}
+__device__ __forceinline__ void apply_bias_impulse(EnvRef e, int b, vec2 j, vec2 r)
+{
+    double minv = BF(e, b, B_MINV), iinv = BF(e, b, B_IINV);
+    BF(e, b, B_VBX) = BF(e, b, B_VBX) + j.x * minv;
+    BF(e, b, B_VBY) = BF(e, b, B_VBY) + j.y * minv;
+    BF(e, b, B_WB) = BF(e, b, B_WB) + iinv * vcross(r, j);
+}
+__device__ __forceinline__ double k_scalar_body(EnvRef e, int b, vec2 r, vec2 n)
+{
+    double rcn = vcross(r, n);
+    return BF(e, b, B_MINV) + BF(e, b, B_IINV) * rcn * rcn;
+}
+__device__ __forceinline__ double k_scalar(EnvRef e, int a, int b, vec2 r1, vec2 r2, vec2 n)
+{
+    return k_scalar_body(e, a, r1, n) + k_scalar_body(e, b, r2, n);
+}
+__device__ __forceinline__ vec2 vclamp_len(vec2 v, double len)
+{
+    if (vdot(v, v) > len * len) {
+        double l = sqrt(vdot(v, v));
+        return vmul(vmul(v, 1.0 / (l + MG_DBL_MIN)), len);
+    }
+    return v;
+}
+__device__ __forceinline__ void set_angle(EnvRef e, int b, double a)
+{
+    double s, c;
+    sincos(a, &s, &c);
+    BF(e, b, B_A) = a; BF(e, b, B_RX) = c; BF(e, b, B_RY) = s;
+}
+
+/* ------------------------------------------------------------------ joints (cpPivotJoint.c, cpGearJoint.c,
+ * cpDampedRotarySpring.c, cpRotaryLimitJoint.c, cpSimpleMotor.c) */
+
+__device__ void con_prestep(EnvRef e, int c)
+{
+    const double dt = MG_DT;
+    int info = IF(e, I_CON0 + c);
+    int kind = info & 255, a = (info >> 8) & 255, b = (info >> 16) & 255;
+    switch (kind) {
+    case CON_PIVOT: {
+        vec2 anchor_a = V(CF(e, c, C_P0), CF(e, c, C_P1));
+        vec2 r1 = vrot(anchor_a, body_rot(e, a));
+        vec2 r2 = vrot(V(0.0, 0.0), body_rot(e, b));
+        double m_sum = BF(e, a, B_MINV) + BF(e, b, B_MINV);
+        double k11 = m_sum, k12 = 0.0, k21 = 0.0, k22 = m_sum;
+        double ai = BF(e, a, B_IINV);
+        double r1xsq = r1.x * r1.x * ai, r1ysq = r1.y * r1.y * ai, r1nxy = -r1.x * r1.y * ai;
+        k11 += r1ysq; k12 += r1nxy; k21 += r1nxy; k22 += r1xsq;
+        double bi = BF(e, b, B_IINV);
+        double r2xsq = r2.x * r2.x * bi, r2ysq = r2.y * r2.y * bi, r2nxy = -r2.x * r2.y * bi;
+        k11 += r2ysq; k12 += r2nxy; k21 += r2nxy; k22 += r2xsq;
+        double det_inv = 1.0 / (k11 * k22 - k12 * k21);
+        CF(e, c, C_K0) = k22 * det_inv; CF(e, c, C_K1) = -k12 * det_inv;
+        CF(e, c, C_K2) = -k21 * det_inv; CF(e, c, C_K3) = k11 * det_inv;
+        CF(e, c, C_R1X) = r1.x; CF(e, c, C_R1Y) = r1.y; CF(e, c, C_R2X) = r2.x; CF(e, c, C_R2Y) = r2.y;
+        vec2 delta = vsub(vadd(body_p(e, b), r2), vadd(body_p(e, a), r1));
+        vec2 bias = vclamp_len(vmul(delta, -CF(e, c, C_BC) / dt), CF(e, c, C_MAXBIAS));
+        CF(e, c, C_BIASX) = bias.x; CF(e, c, C_BIASY) = bias.y;
+        break;
+    }
+    case CON_GEAR: {
+        double phase = CF(e, c, C_P0), ratio = CF(e, c, C_P1), mb = CF(e, c, C_MAXBIAS);
+        double ratio_inv = 1.0 / ratio;
+        CF(e, c, C_ISUM) = 1.0 / (BF(e, a, B_IINV) * ratio_inv + ratio * BF(e, b, B_IINV));
+        CF(e, c, C_BIASX) = dclamp(-CF(e, c, C_BC) * (BF(e, b, B_A) * ratio - BF(e, a, B_A) - phase) / dt, -mb, mb);
+        break;
+    }
+    case CON_SPRING: {
+        double moment = BF(e, a, B_IINV) + BF(e, b, B_IINV);
+        CF(e, c, C_ISUM) = 1.0 / moment;
+        CF(e, c, C_BIASY) = 0.0; /* target_wrn */
+        double j_spring = (((BF(e, a, B_A) - BF(e, b, B_A)) - 0.0) * 0.1) * dt; /* rest 0, stiffness 0.1 (entities.py:273) */
+        CF(e, c, C_JX) = j_spring;
+        BF(e, a, B_W) = BF(e, a, B_W) - j_spring * BF(e, a, B_IINV);
+        BF(e, b, B_W) = BF(e, b, B_W) + j_spring * BF(e, b, B_IINV);
+        break;
+    }
+    case CON_LIMIT: {
+        double lo = CF(e, c, C_P0), hi = CF(e, c, C_P1), mb = CF(e, c, C_MAXBIAS);
+        double dist = BF(e, b, B_A) - BF(e, a, B_A);
+        double pdist = 0.0;
+        if (dist > hi) pdist = hi - dist;
+        else if (dist < lo) pdist = lo - dist;
+        CF(e, c, C_ISUM) = 1.0 / (BF(e, a, B_IINV) + BF(e, b, B_IINV));
+        double bias = dclamp(-CF(e, c, C_BC) * pdist / dt, -mb, mb);
+        CF(e, c, C_BIASX) = bias;
+        if (!bias) CF(e, c, C_JX) = 0.0;
+        break;
+    }
+    case CON_MOTOR:
+        CF(e, c, C_ISUM) = 1.0 / (BF(e, a, B_IINV) + BF(e, b, B_IINV));
+        break;
+    }
+}
+
+__device__ void con_apply_cached(EnvRef e, int c, double dt_coef)
+{
+    int info = IF(e, I_CON0 + c);
+    int kind = info & 255, a = (info >> 8) & 255, b = (info >> 16) & 255;
+    switch (kind) {
+    case CON_PIVOT:
+        apply_impulses(e, a, b, V(CF(e, c, C_R1X), CF(e, c, C_R1Y)), V(CF(e, c, C_R2X), CF(e, c, C_R2Y)),
+                       vmul(V(CF(e, c, C_JX), CF(e, c, C_JY)), dt_coef));
+        break;
+    case CON_GEAR: {
+        double j = CF(e, c, C_JX) * dt_coef;
+        BF(e, a, B_W) = BF(e, a, B_W) - j * BF(e, a, B_IINV) * (1.0 / CF(e, c, C_P1));
+        BF(e, b, B_W) = BF(e, b, B_W) + j * BF(e, b, B_IINV);
+        break;
+    }
+    case CON_SPRING: break;
+    case CON_LIMIT:
+    case CON_MOTOR: {
+        double j = CF(e, c, C_JX) * dt_coef;
+        BF(e, a, B_W) = BF(e, a, B_W) - j * BF(e, a, B_IINV);
+        BF(e, b, B_W) = BF(e, b, B_W) + j * BF(e, b, B_IINV);
+        break;
+    }
+    }
+}
+
+__device__ void con_apply_impulse(EnvRef e, int c)
+{
+    int info = IF(e, I_CON0 + c);
+    int kind = info & 255, a = (info >> 8) & 255, b = (info >> 16) & 255;
+    double j_max = CF(e, c, C_JMAX);
+    switch (kind) {
+    case CON_PIVOT: {
+        vec2 r1 = V(CF(e, c, C_R1X), CF(e, c, C_R1Y)), r2 = V(CF(e, c, C_R2X), CF(e, c, C_R2Y));
+        vec2 vr = relative_velocity(e, a, b, r1, r2);
+        vec2 d = vsub(V(CF(e, c, C_BIASX), CF(e, c, C_BIASY)), vr);
+        vec2 j = V(d.x * CF(e, c, C_K0) + d.y * CF(e, c, C_K1), d.x * CF(e, c, C_K2) + d.y * CF(e, c, C_K3));
+        vec2 j_old = V(CF(e, c, C_JX), CF(e, c, C_JY));
+        vec2 j_acc = vclamp_len(vadd(j_old, j), j_max);
+        CF(e, c, C_JX) = j_acc.x; CF(e, c, C_JY) = j_acc.y;
+        apply_impulses(e, a, b, r1, r2, vsub(j_acc, j_old));
+        break;
+    }
+    case CON_GEAR: {
+        double ratio = CF(e, c, C_P1);
+        double wr = BF(e, b, B_W) * ratio - BF(e, a, B_W);
+        double j = (CF(e, c, C_BIASX) - wr) * CF(e, c, C_ISUM);
+        double j_old = CF(e, c, C_JX);
+        double j_acc = dclamp(j_old + j, -j_max, j_max);
+        CF(e, c, C_JX) = j_acc;
+        j = j_acc - j_old;
+        BF(e, a, B_W) = BF(e, a, B_W) - j * BF(e, a, B_IINV) * (1.0 / ratio);
+        BF(e, b, B_W) = BF(e, b, B_W) + j * BF(e, b, B_IINV);
+        break;
+    }
+    case CON_SPRING: {
+        double wrn = BF(e, a, B_W) - BF(e, b, B_W);
+        double w_damp = (CF(e, c, C_BIASY) - wrn) * CF(e, c, C_P0);
+        CF(e, c, C_BIASY) = wrn + w_damp;
+        double j_damp = w_damp * CF(e, c, C_ISUM);
+        CF(e, c, C_JX) = CF(e, c, C_JX) + j_damp;
+        BF(e, a, B_W) = BF(e, a, B_W) + j_damp * BF(e, a, B_IINV);
+        BF(e, b, B_W) = BF(e, b, B_W) - j_damp * BF(e, b, B_IINV);
+        break;
+    }
+    case CON_LIMIT: {
+        double bias = CF(e, c, C_BIASX);
+        if (!bias) return;
+        double wr = BF(e, b, B_W) - BF(e, a, B_W);
+        double j = -(bias + wr) * CF(e, c, C_ISUM);
+        double j_old = CF(e, c, C_JX), j_acc;
+        if (bias < 0.0) j_acc = dclamp(j_old + j, 0.0, j_max);
+        else j_acc = dclamp(j_old + j, -j_max, 0.0);
+        CF(e, c, C_JX) = j_acc;
+        j = j_acc - j_old;
+        BF(e, a, B_W) = BF(e, a, B_W) - j * BF(e, a, B_IINV);
+        BF(e, b, B_W) = BF(e, b, B_W) + j * BF(e, b, B_IINV);
+        break;
+    }
+    case CON_MOTOR: {
+        double wr = BF(e, b, B_W) - BF(e, a, B_W) + CF(e, c, C_P0);
+        double j = -wr * CF(e, c, C_ISUM);
+        double j_old = CF(e, c, C_JX);
+        double j_acc = dclamp(j_old + j, -j_max, j_max);
+        CF(e, c, C_JX) = j_acc;
+        j = j_acc - j_old;
+        BF(e, a, B_W) = BF(e, a, B_W) - j * BF(e, a, B_IINV);
+        BF(e, b, B_W) = BF(e, b, B_W) + j * BF(e, b, B_IINV);
+        break;
+    }
+    }
+}
+
+/* ------------------------------------------------------------------ collision + arbiters (cpSpaceStep.c, cpArbiter.c) */
+
+__device__ __forceinline__ double shape_friction(int tpl)
+{
+    if (tpl >= MG_TPL_WALL0) return 0.8;                       /* entities.py:521 */
+    if (tpl < MG_TPL_SQUARE) return 5.0;                       /* fingers, entities.py:369 */
+    return 0.5;                                                /* robot body :358, blocks :696-698 */
+}
+
+__device__ __forceinline__ double shape_bound(const MgTables *T, int tpl)
+{
+    if (tpl >= MG_TPL_CIRCLE_ROBOT) return tpl == MG_TPL_CIRCLE_ROBOT ? 0.2 : 0.2 * 0.6;
+    return T->tpl_bound[tpl];
+}
+
+/* cpSpaceCollideShapes + cpArbiterUpdate for shapes i < j (add order); returns the arbiter slot or -1 */
+__device__ int collide_pair(EnvRef e, int i, int j, int info_i, int info_j, const WShape *Si, const WShape *Sj, int stamp)
+{
+    int sa = i, sb = j, ia = info_i, ib = info_j;
+    const WShape *A = Si, *B = Sj;
+    if (Si->kind > Sj->kind) { sa = j; sb = i; ia = info_j; ib = info_i; A = Sj; B = Si; }
+    Manifold m;
+    if (collide_shapes(A, B, &m) == 0) return -1;
+    int ba = (ia >> 8) & 255, bb = (ib >> 8) & 255;
+    int key = sa | (sb << 8);
+    int n_arbs = IF(e, I_NARBS), slot = -1;
+    for (int q = 0; q < n_arbs; q++)
+        if ((AIF(e, q, AI_KEY) & 0xffff) == key) { slot = q; break; }
+    int state = ARB_FIRST, old_count = 0;
+    uint32_t old_hash[2] = { 0, 0 };
+    double old_jn[2] = { 0, 0 }, old_jt[2] = { 0, 0 };
+    if (slot < 0) {
+        if (n_arbs >= MG_NARB) return -1;
+        slot = n_arbs;
+        IF(e, I_NARBS) = n_arbs + 1;
+    } else {
+        int fl = AIF(e, slot, AI_FLAGS);
+        state = fl & 255; old_count = (fl >> 8) & 255;
+        uint32_t hh = (uint32_t)AIF(e, slot, AI_HASH);
+        old_hash[0] = hh & 0xffff; old_hash[1] = hh >> 16;
+        for (int q = 0; q < old_count; q++) { old_jn[q] = ACF(e, slot, q, AC_JN); old_jt[q] = ACF(e, slot, q, AC_JT); }
+    }
+    vec2 pa = body_p(e, ba), pb = body_p(e, bb);
+    for (int k = 0; k < m.count; k++) {
+        vec2 r1 = vsub(m.p1[k], pa), r2 = vsub(m.p2[k], pb);
+        double jn = 0.0, jt = 0.0;
+        for (int q = 0; q < old_count; q++)
+            if (m.hash[k] == old_hash[q]) { jn = old_jn[q]; jt = old_jt[q]; }
+        ACF(e, slot, k, AC_R1X) = r1.x; ACF(e, slot, k, AC_R1Y) = r1.y;
+        ACF(e, slot, k, AC_R2X) = r2.x; ACF(e, slot, k, AC_R2Y) = r2.y;
+        ACF(e, slot, k, AC_JN) = jn; ACF(e, slot, k, AC_JT) = jt;
+    }
+    AF(e, slot, A_NX) = m.n.x; AF(e, slot, A_NY) = m.n.y;
+    AF(e, slot, A_U) = shape_friction(ia & 255) * shape_friction(ib & 255);
+    if (state == ARB_CACHED) state = ARB_FIRST;
+    AIF(e, slot, AI_KEY) = key | (ba << 16) | (bb << 24);
+    AIF(e, slot, AI_STAMP) = stamp;
+    AIF(e, slot, AI_FLAGS) = state | (m.count << 8) | (1 << 16);
+    AIF(e, slot, AI_HASH) = (int)(m.hash[0] | (m.count > 1 ? m.hash[1] << 16 : 0u));
+    return slot;
+}
+
+__device__ void arb_prestep(EnvRef e, int s, double slop, double bias_c)
+{
+    const double dt = MG_DT;
+    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
+    int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
+    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    vec2 body_delta = vsub(body_p(e, b), body_p(e, a));
+    for (int k = 0; k < count; k++) {
+        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
+        ACF(e, s, k, AC_NMASS) = 1.0 / k_scalar(e, a, b, r1, r2, n);
+        ACF(e, s, k, AC_TMASS) = 1.0 / k_scalar(e, a, b, r1, r2, vperp(n));
+        double dist = vdot(vadd(vsub(r2, r1), body_delta), n);
+        ACF(e, s, k, AC_BIAS) = -bias_c * fmin(0.0, dist + slop) / dt;
+        ACF(e, s, k, AC_JBIAS) = 0.0;
+        /* bounce = normal_relative_velocity * e with e = 0 for every shape */
+    }
+}
+
+__device__ void arb_apply_cached(EnvRef e, int s, double dt_coef)
+{
+    int fl = AIF(e, s, AI_FLAGS);
+    if ((fl & 255) == ARB_FIRST) return;
+    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
+    int count = (fl >> 8) & 255;
+    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    for (int k = 0; k < count; k++) {
+        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
+        vec2 j = vrot(n, V(ACF(e, s, k, AC_JN), ACF(e, s, k, AC_JT)));
+        apply_impulses(e, a, b, r1, r2, vmul(j, dt_coef));
+    }
+}
+
+__device__ void arb_apply_impulse(EnvRef e, int s)
+{
+    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
+    int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
+    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    double friction = AF(e, s, A_U);
+    for (int k = 0; k < count; k++) {
+        double n_mass = ACF(e, s, k, AC_NMASS);
+        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
+        vec2 vb1 = vadd(V(BF(e, a, B_VBX), BF(e, a, B_VBY)), vmul(vperp(r1), BF(e, a, B_WB)));
+        vec2 vb2 = vadd(V(BF(e, b, B_VBX), BF(e, b, B_VBY)), vmul(vperp(r2), BF(e, b, B_WB)));
+        vec2 vr = relative_velocity(e, a, b, r1, r2);
+        double vbn = vdot(vsub(vb2, vb1), n);
+        double vrn = vdot(vr, n);
+        double vrt = vdot(vr, vperp(n));
+        double jbn = (ACF(e, s, k, AC_BIAS) - vbn) * n_mass;
+        double jbn_old = ACF(e, s, k, AC_JBIAS);
+        double j_bias = fmax(jbn_old + jbn, 0.0);
+        ACF(e, s, k, AC_JBIAS) = j_bias;
+        double jn = -(0.0 + vrn) * n_mass;
+        double jn_old = ACF(e, s, k, AC_JN);
+        double jn_acc = fmax(jn_old + jn, 0.0);
+        ACF(e, s, k, AC_JN) = jn_acc;
+        double jt_max = friction * jn_acc;
+        double jt = -vrt * ACF(e, s, k, AC_TMASS);
+        double jt_old = ACF(e, s, k, AC_JT);
+        double jt_acc = dclamp(jt_old + jt, -jt_max, jt_max);
+        ACF(e, s, k, AC_JT) = jt_acc;
+        vec2 jb = vmul(n, j_bias - jbn_old);
+        apply_bias_impulse(e, a, vneg(jb), r1);
+        apply_bias_impulse(e, b, jb, r2);
+        apply_impulses(e, a, b, r1, r2, vrot(n, V(jn_acc - jn_old, jt_acc - jt_old)));
+    }
+}
+
+__device__ void arb_copy(EnvRef e, int dst, int src)
+{
+    for (int f = 0; f < A_NF; f++) AF(e, dst, f) = AF(e, src, f);
+    for (int f = 0; f < 4; f++) AIF(e, dst, f) = AIF(e, src, f);
+}
+
+/* cpSpaceStep(space, dt) */
+__device__ void space_step(EnvRef e, const MgTables *T)
+{
+    const double dt = MG_DT;
+    int prev_stamp = IF(e, I_STAMP);
+    int stamp = prev_stamp + 1;
+    IF(e, I_STAMP) = stamp;
+
+    /* cpSpaceArbiterSetFilter of the previous step (same effect as running it at the end of
+     * that step) merged with this step's arbiter-list reset */
+    {
+        int n_arbs = IF(e, I_NARBS), w = 0;
+        for (int q = 0; q < n_arbs; q++) {
+            int fl = AIF(e, q, AI_FLAGS);
+            int ticks = prev_stamp - AIF(e, q, AI_STAMP);
+            int state = fl & 255;
+            if ((fl >> 16) & 1) state = ARB_NORMAL;
+            if (ticks >= 1 && state != ARB_CACHED) state = ARB_CACHED;
+            if (ticks >= 3) continue;                     /* collision_persistence = 3 */
+            AIF(e, q, AI_FLAGS) = state | (fl & 0xff00);  /* live cleared */
+            if (w != q) arb_copy(e, w, q);
+            w++;
+        }
+        IF(e, I_NARBS) = w;
+    }
+
+    /* cpBodyUpdatePosition for dynamic and kinematic bodies */
+    int nb = IF(e, I_NBODIES);
+    for (int b = 1; b < nb; b++) {
+        BF(e, b, B_PX) = BF(e, b, B_PX) + (BF(e, b, B_VX) + BF(e, b, B_VBX)) * dt;
+        BF(e, b, B_PY) = BF(e, b, B_PY) + (BF(e, b, B_VY) + BF(e, b, B_VBY)) * dt;
+        set_angle(e, b, BF(e, b, B_A) + (BF(e, b, B_W) + BF(e, b, B_WB)) * dt);
+        BF(e, b, B_VBX) = 0.0; BF(e, b, B_VBY) = 0.0; BF(e, b, B_WB) = 0.0;
+    }
+
+    /* narrow phase over shape pairs in add order (i < j) */
+    unsigned char order[MG_NARB];
+    int n_live = 0;
+    int ns = IF(e, I_NSHAPES);
+    for (int i = 0; i < ns; i++) {
+        int info_i = IF(e, I_SHAPE0 + i);
+        int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
+        vec2 pi = body_p(e, body_i);
+        double ri = shape_bound(T, tpl_i);
+        WShape Si;
+        bool have_i = false;
+        for (int j = i + 1; j < ns; j++) {
+            int info_j = IF(e, I_SHAPE0 + j);
+            int ent_j = info_j >> 16;
+            if (ent_i == ent_j) continue;  /* same body, ShapeFilter group (robot: 1, star pieces), static-static */
+            int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
+            vec2 pj = body_p(e, body_j);
+            double rj = shape_bound(T, tpl_j) + 1e-6;
+            if (tpl_i >= MG_TPL_WALL0) {
+                /* wall i (radius 1) against the bounding circle of shape j */
+                int w = tpl_i - MG_TPL_WALL0;
+                vec2 wa = T->wall_a[w], wb = T->wall_b[w];
+                if (fmin(wa.x, wb.x) - 1.0 > pj.x + rj || fmax(wa.x, wb.x) + 1.0 < pj.x - rj ||
+                    fmin(wa.y, wb.y) - 1.0 > pj.y + rj || fmax(wa.y, wb.y) + 1.0 < pj.y - rj) continue;
+            } else {
+                vec2 d = vsub(pj, pi);
+                double rr = ri + rj;
+                if (vdot(d, d) > rr * rr) continue;
+            }
+            if (!have_i) { wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), &Si); have_i = true; }
+            WShape Sj;
+            wshape_from_tpl(T, tpl_j, pj, body_rot(e, body_j), &Sj);
+            int slot = collide_pair(e, i, j, info_i, info_j, &Si, &Sj, stamp);
+            if (slot >= 0) order[n_live++] = (unsigned char)slot;
+        }
+    }
+
+    /* pre-step */
+    const double slop = 0.01;                       /* base_env.py:207 */
+    const double bias_c = T->bias_coef_default;     /* 1 - collision_bias^dt */
+    for (int q = 0; q < n_live; q++) arb_prestep(e, order[q], slop, bias_c);
+    int nc = IF(e, I_NCON);
+    for (int c = 0; c < nc; c++) con_prestep(e, c);
+
+    /* cpBodyUpdateVelocity: gravity 0, damping 1, no forces -> identity */
+
+    double dt_coef = IF(e, I_STEPPED) ? 1.0 : 0.0;  /* prev_dt == 0 ? 0 : dt / prev_dt */
+    IF(e, I_STEPPED) = 1;
+    for (int q = 0; q < n_live; q++) arb_apply_cached(e, order[q], dt_coef);
+    for (int c = 0; c < nc; c++) con_apply_cached(e, c, dt_coef);
+
+    for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
+        for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order[q]);
+        for (int c = 0; c < nc; c++) con_apply_impulse(e, c);
+    }
+}
+
+/* ------------------------------------------------------------------ scores (magical/benchmarks/*.py score_on_end_of_traj) */
+
+__device__ __forceinline__ vec2 block_pos(EnvRef e, int bi) { return body_p(e, MG_BODY_BLOCK0 + bi); }
+__device__ __forceinline__ vec2 robot_pos(EnvRef e) { return body_p(e, MG_BODY_ROBOT); }
+
+/* goal sensor shape: Poly.create_box(body, (w, h)) on a static body at (cx, cy) (entities.py:783-791) */
+__device__ void goal_shape(EnvRef e, int g, WShape *s, double *bb)
+{
+    double cx = DF(e, D_GOAL0 + g * 4 + 0), cy = DF(e, D_GOAL0 + g * 4 + 1);
+    double h = DF(e, D_GOAL0 + g * 4 + 2), w = DF(e, D_GOAL0 + g * 4 + 3);
+    double hw = w / 2, hh = h / 2;
+    vec2 lv[4] = { V(hw, -hh), V(hw, hh), V(-hw, hh), V(-hw, -hh) };
+    s->kind = MG_SHAPE_POLY; s->n = 4; s->r = 0.0;
+    double l = INFINITY, r = -INFINITY, bo = INFINITY, t = -INFINITY;
+    for (int i = 0; i < 4; i++) {
+        vec2 a = lv[(i + 3) % 4], b = lv[i];
+        double dx = b.x - a.x, dy = b.y - a.y;
+        double nx = dy, ny = -dx;
+        double inv = 1.0 / (sqrt(nx * nx + ny * ny) + MG_DBL_MIN);
+        vec2 ln = V(nx * inv, ny * inv);
+        vec2 wv = V(1.0 * b.x - 0.0 * b.y + cx, 0.0 * b.x + 1.0 * b.y + cy);
+        s->v[i] = wv;
+        s->nrm[i] = V(1.0 * ln.x - 0.0 * ln.y, 0.0 * ln.x + 1.0 * ln.y);
+        l = fmin(l, wv.x); r = fmax(r, wv.x); bo = fmin(bo, wv.y); t = fmax(t, wv.y);
+    }
+    bb[0] = l; bb[1] = bo; bb[2] = r; bb[3] = t;
+}
+
+/* GoalRegion.get_overlapping_ents(com_overlap=True) over the block index (entities.py:803-863):
+ * bit bi set iff every shape of block bi touches the goal box and the block's body position
+ * lies in the goal's AABB. */
+__device__ unsigned goal_overlaps(EnvRef e, const MgTables *T, int g)
+{
+    WShape G;
+    double bb[4];
+    goal_shape(e, g, &G, bb);
+    unsigned mask = 0;
+    int ns = IF(e, I_NSHAPES), nbk = IF(e, I_NBLOCKS);
+    for (int bi = 0; bi < nbk; bi++) {
+        vec2 p = block_pos(e, bi);
+        bool com_in = bb[0] <= p.x && bb[2] >= p.x && bb[1] <= p.y && bb[3] >= p.y;
+        bool all = com_in;
+        if (com_in) {
+            for (int s = 0; s < ns && all; s++) {
+                int info = IF(e, I_SHAPE0 + s);
+                if ((info >> 16) != MG_ENTID_BLOCK0 + bi) continue;
+                WShape S;
+                int body = (info >> 8) & 255;
+                wshape_from_tpl(T, info & 255, body_p(e, body), body_rot(e, body), &S);
+                Manifold m;
+                int cnt = S.kind <= G.kind ? collide_shapes(&S, &G, &m) : collide_shapes(&G, &S, &m);
+                if (cnt == 0) all = false;
+            }
+        }
+        if (all) mask |= 1u << bi;
+    }
+    return mask;
+}
+
+__device__ double score_move_to_corner(EnvRef e)                 /* move_to_corner.py:67-77 */
+{
+    vec2 p = robot_pos(e);
+    double dx = -1.0 - p.x, dy = 1.0 - p.y;
+    double dist = sqrt(dx * dx + dy * dy);
+    double succeed_dist = sqrt(2.0) / 2, furthest_dist = sqrt(2.0);
+    double drange = furthest_dist - succeed_dist;
+    return fmin(1.0, fmax(0.0, furthest_dist - dist) / drange);
+}
+
+__device__ double score_move_to_region(EnvRef e)                 /* move_to_region.py:85-94 */
+{
+    WShape G; double bb[4];
+    goal_shape(e, 0, &G, bb);
+    vec2 p = robot_pos(e);
+    double maxd = -INFINITY;
+    for (int i = 0; i < 4; i++) maxd = fmax(maxd, (p.x - G.v[i].x) * G.nrm[i].x + (p.y - G.v[i].y) * G.nrm[i].y);
+    return maxd <= 0.0 ? 1.0 : 0.0;
+}
+
+__device__ __forceinline__ int block_role(EnvRef e, int bi) { return (IF(e, I_BLOCK0 + bi) >> 16) & 255; }
+
+__device__ double score_match_regions(EnvRef e, const MgTables *T) /* match_regions.py:193-213 */
+{
+    unsigned ov = goal_overlaps(e, T, 0);
+    int n_t = 0, n_ot = 0, n_od = 0, n_o = 0, nbk = IF(e, I_NBLOCKS);
+    for (int i = 0; i < nbk; i++) {
+        int role = block_role(e, i);
+        if (role == MG_ROLE_TARGET) n_t++;
+        if (ov >> i & 1) { n_o++; if (role == MG_ROLE_TARGET) n_ot++; if (role == MG_ROLE_DISTRACTOR) n_od++; }
+    }
+    double target_frac_done = (double)n_ot / (double)n_t;
+    double contamination = n_o == 0 ? 0.0 : (double)n_od / (double)n_o;
+    return target_frac_done * (1 - contamination);
+}
+
+__device__ double score_find_dupe(EnvRef e, const MgTables *T)    /* find_dupe.py:203-216 */
+{
+    unsigned ov = goal_overlaps(e, T, 0);
+    int n_ot = 0, n_od = 0, n_o = 0, nbk = IF(e, I_NBLOCKS);
+    for (int i = 0; i < nbk; i++) {
+        if (!(ov >> i & 1)) continue;
+        n_o++;
+        int role = block_role(e, i);
+        if (role == MG_ROLE_TARGET) n_ot++;
+        if (role == MG_ROLE_DISTRACTOR) n_od++;
+    }
+    double have_two = n_ot >= 2 ? 1.0 : 0.0;
+    double contamination = n_o == 0 ? 0.0 : (double)n_od / (double)n_o;
+    return have_two * (1 - contamination);
+}
+
+__device__ double score_fix_colour(EnvRef e, const MgTables *T)   /* fix_colour.py:193-202 */
+{
+    int ng = IF(e, I_NGOALS);
+    for (int g = 0; g < ng; g++) {
+        unsigned ov = goal_overlaps(e, T, g);
+        int want = ((IF(e, I_GOAL0 + g) >> 8) & 255) - 1;
+        bool ok = want < 0 ? ov == 0 : ov == (1u << want);
+        if (!ok) return 0.0;
+    }
+    return 1.0;
+}
+
+/* make_line.longest_line (make_line.py:31-71) */
+__device__ int longest_line(const vec2 *pts, int npts, double inlier_dist, double max_sep)
+{
+    int best = npts < 1 ? npts : 1;
+    for (int i = 0; i < npts - 1; i++)
+        for (int j = i + 1; j < npts; j++) {
+            vec2 pi = pts[i];
+            vec2 off_j = vsub(pts[j], pi);
+            double nrm = sqrt(off_j.x * off_j.x + off_j.y * off_j.y);
+            vec2 u = V(off_j.x / nrm, off_j.y / nrm);
+            double inl[MG_MAX_BLOCKS];
+            int n_in = 0;
+            for (int k = 0; k < npts; k++) {
+                vec2 off = vsub(pts[k], pi);
+                double proj = off.x * u.x + off.y * u.y;
+                double rx = off.x - proj * u.x, ry = off.y - proj * u.y;
+                if (sqrt(rx * rx + ry * ry) <= inlier_dist) inl[n_in++] = proj;
+            }
+            if (n_in <= best) continue;
+            for (int a = 1; a < n_in; a++) {          /* np.sort */
+                double x = inl[a]; int b = a - 1;
+                while (b >= 0 && inl[b] > x) { inl[b + 1] = inl[b]; b--; }
+                inl[b + 1] = x;
+            }
+            int max_run = 0, run = 0;
+            for (int k = 0; k + 1 < n_in; k++) {
+                if (fabs(inl[k + 1] - inl[k]) <= max_sep) { run++; if (run > max_run) max_run = run; }
+                else run = 0;
+            }
+            max_run += 1;
+            if (max_run > best) best = max_run;
+        }
+    return best;
+}
+
+__device__ double score_make_line(EnvRef e)                      /* make_line.py:142-152 */
+{
+    const double SHAPE_RAD = 0.2 * 0.6;
+    vec2 pts[MG_MAX_BLOCKS];
+    int n = IF(e, I_NBLOCKS);
+    for (int i = 0; i < n; i++) pts[i] = block_pos(e, i);
+    int line_len = longest_line(pts, n, SHAPE_RAD * 1.5, SHAPE_RAD * 3.5);
+    int min_len = n - 2 > 2 ? n - 2 : 2;
+    int num = line_len - min_len > 0 ? line_len - min_len : 0;
+    return (double)num / (double)(n - min_len);
+}
+
+/* cluster.py:166-216; characteristic values in np.unique (string-sorted) order */
+__device__ double score_cluster(EnvRef e, int by_type)
+{
+    const int colour_rank[4] = { 2, 1, 0, 3 };   /* red, green, blue, yellow -> blue<green<red<yellow */
+    const int type_rank[4] = { 2, 1, 3, 0 };     /* square, pentagon, star, circle -> circle<pentagon<square<star */
+    int n = IF(e, I_NBLOCKS);
+    int label[MG_MAX_BLOCKS], present[4] = { 0, 0, 0, 0 };
+    for (int i = 0; i < n; i++) {
+        int info = IF(e, I_BLOCK0 + i);
+        label[i] = by_type ? type_rank[info & 255] : colour_rank[(info >> 8) & 255];
+        present[label[i]] = 1;
+    }
+    int idx_of[4], nvals = 0;
+    for (int r = 0; r < 4; r++) idx_of[r] = present[r] ? nvals++ : -1;
+    vec2 cent[4];
+    for (int r = 0; r < 4; r++) {
+        if (!present[r]) continue;
+        double sx = 0.0, sy = 0.0; int cnt = 0;
+        for (int i = 0; i < n; i++) if (label[i] == r) { vec2 p = block_pos(e, i); sx += p.x; sy += p.y; cnt++; }
+        cent[idx_of[r]] = V(sx / cnt, sy / cnt);
+    }
+    int n_blocks = 0, n_correct = 0;
+    for (int r = 0; r < 4; r++) {
+        if (!present[r]) continue;
+        for (int i = 0; i < n; i++) {
+            if (label[i] != r) continue;
+            n_blocks++;
+            vec2 p = block_pos(e, i);
+            double true_sse = 0.0, nearest_bad = INFINITY;
+            for (int c = 0; c < nvals; c++) {
+                double dx = p.x - cent[c].x, dy = p.y - cent[c].y;
+                double sse = dx * dx + dy * dy;
+                if (c == idx_of[r]) true_sse = sse;
+                else if (sse < nearest_bad) nearest_bad = sse;
+            }
+            n_correct += sqrt(true_sse) < sqrt(nearest_bad) - 2.0 * true_sse ? 1 : 0;
+        }
+    }
+    double frac = (double)n_correct / (double)(n_blocks > 1 ? n_blocks : 1);
+    return fmax(frac - 0.75, 0.0) / (1 - 0.75);
+}
+
+__device__ double score_pick_and_place(EnvRef e)                 /* pick_and_place.py:88-102 */
+{
+    const double SHAPE_RAD = 0.2 * 0.6;
+    double best = -1e9;
+    int nv = IF(e, I_NVALID);
+    for (int k = 0; k < nv; k++) {
+        vec2 sp = block_pos(e, IF(e, I_TARGET_BLOCK));
+        double dx = DF(e, D_TARGET) - sp.x, dy = DF(e, D_TARGET + 1) - sp.y;
+        double dist = sqrt(dx * dx + dy * dy);
+        double furthest = sqrt(2.0);
+        double drange = furthest - SHAPE_RAD;
+        best = fmax(best, fmin(1.0, fmax(0.0, furthest - dist) / drange));
+    }
+    return best;
+}
+
+__device__ double env_score(EnvRef e, const MgTables *T)
+{
+    switch (IF(e, I_TASK)) {
+    case MG_TASK_MOVE_TO_CORNER: return score_move_to_corner(e);
+    case MG_TASK_MOVE_TO_REGION: return score_move_to_region(e);
+    case MG_TASK_MATCH_REGIONS: return score_match_regions(e, T);
+    case MG_TASK_MAKE_LINE: return score_make_line(e);
+    case MG_TASK_FIND_DUPE: return score_find_dupe(e, T);
+    case MG_TASK_FIX_COLOUR: return score_fix_colour(e, T);
+    case MG_TASK_CLUSTER_COLOUR: return score_cluster(e, 0);
+    case MG_TASK_CLUSTER_SHAPE: return score_cluster(e, 1);
+    case MG_TASK_PICK_AND_PLACE: return score_pick_and_place(e);
+    }
+    return 0.0;
+}
+
+/* move_to_corner.py:86-100, pick_and_place.py:114-124 */
+__device__ double env_debug_reward(EnvRef e)
+{
+    vec2 rp = robot_pos(e);
+    int task = IF(e, I_TASK);
+    if (task == MG_TASK_MOVE_TO_CORNER) {
+        vec2 sp = block_pos(e, 0);
+        double dx = sp.x - 0.0, dy = sp.y - 1.0;
+        double shape_to_corner = sqrt(dx * dx + dy * dy);
+        double rx = rp.x - sp.x, ry = rp.y - sp.y;
+        double robot_to_shape = sqrt(rx * rx + ry * ry);
+        double shaping = -shape_to_corner / 5 - fmax(robot_to_shape, 0.2) / 20;
+        return shaping + score_move_to_corner(e);
+    }
+    if (task == MG_TASK_PICK_AND_PLACE) {
+        const double SHAPE_RAD = 0.2 * 0.6;
+        vec2 sp = block_pos(e, IF(e, I_TARGET_BLOCK));
+        double dx = sp.x - DF(e, D_TARGET), dy = sp.y - DF(e, D_TARGET + 1);
+        double shape_to_target = sqrt(dx * dx + dy * dy);
+        double rx = rp.x - sp.x, ry = rp.y - sp.y;
+        double robot_to_shape = sqrt(rx * rx + ry * ry);
+        double shaping = -shape_to_target / 5 - fmax(robot_to_shape, SHAPE_RAD) / 10;
+        return shaping + score_pick_and_place(e);
+    }
+    return 0.0;
+}
+
+/* ------------------------------------------------------------------ kernels */
+
+/* BaseEnv.step up to (not including) render */
+__global__ void __launch_bounds__(32) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
+                                                        uint8_t *done_out, float *score_out)
+{
+    int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env >= S.num_envs) return;
+    const MgTables *T = S.tables;
+    EnvRef e = env_ref(S.dstate, S.istate, env);
+
+    /* ACTION_ID_TO_FLAGS: id = ud + 3 * lr + 9 * grip (entities.py:148-190); Robot.set_action (:435-453) */
+    int action = actions[env];
+    action = action < 0 ? 0 : (action >= MG_NUM_ACTIONS ? MG_NUM_ACTIONS - 1 : action);
+    int ud = action % 3, lr = (action / 3) % 3, grip = action / 9;
+    const double radius = 0.2;
+    double rel_turn_angle = 0.0, target_speed = 0.0;
+    if (ud == 1) target_speed += 4.0 * radius;
+    if (ud == 2) target_speed -= 3.0 * radius;
+    if (lr == 1) rel_turn_angle += 1.5;
+    if (lr == 2) rel_turn_angle -= 1.5;
+    double target_finger_angle = grip == 0 ? M_PI / 8 : -0.0;
+
+    const int rb = MG_BODY_ROBOT;
+    int motor_l = IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6;  /* robot constraints 0..9: motors are 6 and 9 */
+    for (int sub = 0; sub < 10; sub++) {
+        /* Robot.update (entities.py:455-476) */
+        set_angle(e, rb + MG_RB_CONTROL, BF(e, rb, B_A) + rel_turn_angle);
+        vec2 vel = vrot(body_rot(e, rb), V(0.0, target_speed));
+        BF(e, rb + MG_RB_CONTROL, B_VX) = vel.x; BF(e, rb + MG_RB_CONTROL, B_VY) = vel.y;
+        for (int k = 0; k < 2; k++) {
+            double side = k == 0 ? -1.0 : 1.0;
+            double rel_angle = BF(e, rb + MG_RB_FINGER_L + k, B_A) - BF(e, rb, B_A);
+            double angle_error = rel_angle + side * target_finger_angle;
+            double target_rate = fmax(-1.0, fmin(1.0, angle_error * 10));
+            if (fabs(target_rate) < 1e-4) target_rate = 0.0;
+            CF(e, motor_l + 3 * k, C_P0) = target_rate;
+        }
+        space_step(e, T);
+    }
+
+    int steps = IF(e, I_EPISODE_STEPS) + 1;
+    IF(e, I_EPISODE_STEPS) = steps;
+    bool done = steps >= IF(e, I_HORIZON);
+    double rew = 0.0, eval_score = 0.0;
+    if (done) rew = eval_score = env_score(e, T);
+    if (IF(e, I_DEBUG_REWARD)) rew = env_debug_reward(e);
+    if (reward) reward[env] = (float)rew;
+    if (done_out) done_out[env] = done ? 1 : 0;
+    if (score_out) score_out[env] = (float)eval_score;
+    export_poses(e, S.poses + (size_t)env * MG_POSE_STRIDE);
+}
+
+__global__ void mg_score_kernel(MgDeviceState S, float *out, int debug_reward)
+{
+    int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env >= S.num_envs) return;
+    EnvRef e = env_ref(S.dstate, S.istate, env);
+    out[env] = (float)(debug_reward ? env_debug_reward(e) : env_score(e, S.tables));
+}
+
+/* checkpoint gather / scatter: blob = D_NF doubles then I_NF ints */
+__global__ void mg_state_copy_kernel(MgDeviceState S, const int32_t *env_ids, int n, double *dblobs, int *iblobs, int scatter)
+{
+    int k = blockIdx.x;
+    if (k >= n) return;
+    int env = env_ids ? env_ids[k] : k;
+    EnvRef e = env_ref(S.dstate, S.istate, env);
+    for (int f = threadIdx.x; f < D_NF; f += blockDim.x) {
+        if (scatter) DF(e, f) = dblobs[(size_t)k * D_NF + f]; else dblobs[(size_t)k * D_NF + f] = DF(e, f);
+    }
+    for (int f = threadIdx.x; f < I_NF; f += blockDim.x) {
+        if (scatter) IF(e, f) = iblobs[(size_t)k * I_NF + f]; else iblobs[(size_t)k * I_NF + f] = IF(e, f);
+    }
+    if (scatter) {
+        __syncthreads();
+        if (threadIdx.x == 0) export_poses(e, S.poses + (size_t)env * MG_POSE_STRIDE);
+    }
+}
+
+void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st)
+{
+    if (n <= 0) return;
+    mg_init_kernel<<<(n + 31) / 32, 32, 0, st>>>(S, scenes_dev, env_ids_dev, n);
+}
+void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st)
+{
+    mg_physics_kernel<<<(S.num_envs + 31) / 32, 32, 0, st>>>(S, actions, reward, done, score);
+}
+void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
+{
+    mg_score_kernel<<<(S.num_envs + 31) / 32, 32, 0, st>>>(S, out, debug_reward);
+}
+void mg_launch_state_gather(const MgDeviceState &S, const int32_t *env_ids_dev, int n, double *dblobs, int *iblobs, int scatter, cudaStream_t st)
+{
+    if (n <= 0) return;
+    mg_state_copy_kernel<<<n, 128, 0, st>>>(S, env_ids_dev, n, dblobs, iblobs, scatter);
+}
