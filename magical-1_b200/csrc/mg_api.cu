@@ -1,0 +1,452 @@
+/*
+ * mg_api.cu -- the C ABI of libmagical_b200.so (include/mg_b200.h): handle, device memory,
+ * stream plumbing and the order of kernel launches that makes up reset / step / render.
+ * There is no CPU implementation behind these entry points.
+ */
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "mg_kernels.h"
+#include "mg_tables.h"
+
+struct mg_handle {
+    mg_config cfg;
+    MgDeviceState S;
+    MgObsSpec spec;
+    bool fused;                 /* single-view HWC stack: composed inside the render kernel */
+    int slots[2];               /* newest ring slot per view */
+    MgTables *tables_dev;
+    mg_scene *scene_stage_dev;  /* [B] staging for mg_set_scenes */
+    int32_t *ids_stage_dev;     /* [B] */
+    /* mg_step_host staging */
+    int32_t *actions_dev;
+    uint8_t *obs_dev;
+    float *reward_dev, *score_dev;
+    uint8_t *done_dev;
+    size_t obs_bytes;
+    cudaStream_t own_stream;
+    /* accounting */
+    int64_t launches;
+    int timing;
+    cudaEvent_t ev[4];
+    double ms[2];
+    int64_t timed_launches[2];
+    std::vector<std::pair<int, int>> pending;   /* (which, event pair index) not used: timing is synchronous */
+    std::string err;
+};
+
+static std::string g_create_err;
+
+static int fail(mg_handle *h, int code, const std::string &msg)
+{
+    if (h) h->err = msg; else g_create_err = msg;
+    return code;
+}
+
+#define CK(h, call)                                                                         \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess)                                                              \
+            return fail(h, MG_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+extern "C" const char *mg_last_error(const mg_handle *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
+{
+    if (!cfg || !out) return fail(nullptr, MG_ERR_ARG, "mg_create: null argument");
+    if (cfg->num_envs <= 0) return fail(nullptr, MG_ERR_ARG, "mg_create: num_envs must be positive");
+    if (cfg->n_groups < 0 || cfg->n_groups > MG_MAX_GROUPS) return fail(nullptr, MG_ERR_ARG, "mg_create: bad n_groups");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, MG_ERR_NODEVICE, "mg_create: no CUDA device (this library has no CPU path)");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(nullptr, MG_ERR_ARG, "mg_create: bad device ordinal");
+    mg_handle *h = new mg_handle();
+    h->cfg = *cfg;
+    h->launches = 0; h->timing = 0; h->ms[0] = h->ms[1] = 0; h->timed_launches[0] = h->timed_launches[1] = 0;
+    h->slots[0] = h->slots[1] = 0;
+    memset(&h->S, 0, sizeof(h->S));
+    memset(&h->spec, 0, sizeof(h->spec));
+    h->spec.n_groups = cfg->n_groups; h->spec.chw = cfg->chw;
+    bool single_view = true;
+    for (int g = 0; g < cfg->n_groups; g++) {
+        int v = cfg->group_view[g], a = cfg->group_age[g];
+        if (v < 0 || v > 1 || a < 0 || a >= MG_MAX_RING) { delete h; return fail(nullptr, MG_ERR_ARG, "mg_create: bad group spec"); }
+        h->spec.view[g] = v; h->spec.age[g] = a;
+        h->spec.render_view[v] = 1;
+        if (v != cfg->group_view[0]) single_view = false;
+    }
+    h->fused = cfg->n_groups > 0 && single_view && !cfg->chw;
+    const int B = cfg->num_envs;
+    const size_t groups = (B + MG_GROUP - 1) / MG_GROUP;
+    CK(h, cudaSetDevice(cfg->device));
+    CK(h, cudaMalloc(&h->S.dstate, groups * D_NF * MG_GROUP * sizeof(double)));
+    CK(h, cudaMalloc(&h->S.istate, groups * I_NF * MG_GROUP * sizeof(int)));
+    CK(h, cudaMemset(h->S.dstate, 0, groups * D_NF * MG_GROUP * sizeof(double)));
+    CK(h, cudaMemset(h->S.istate, 0, groups * I_NF * MG_GROUP * sizeof(int)));
+    CK(h, cudaMalloc(&h->S.scenes, (size_t)B * sizeof(mg_scene)));
+    CK(h, cudaMemset(h->S.scenes, 0, (size_t)B * sizeof(mg_scene)));
+    CK(h, cudaMalloc(&h->S.prims, (size_t)B * MG_MAX_PRIMS * sizeof(MgPrim)));
+    CK(h, cudaMalloc(&h->S.n_prims, (size_t)B * sizeof(int)));
+    CK(h, cudaMemset(h->S.n_prims, 0, (size_t)B * sizeof(int)));
+    CK(h, cudaMalloc(&h->S.poses, (size_t)B * MG_POSE_STRIDE * sizeof(double)));
+    CK(h, cudaMemset(h->S.poses, 0, (size_t)B * MG_POSE_STRIDE * sizeof(double)));
+    for (int v = 0; v < 2; v++) {
+        CK(h, cudaMalloc(&h->S.ring[v], (size_t)B * MG_MAX_RING * MG_FRAME_BYTES));
+        CK(h, cudaMemset(h->S.ring[v], 0, (size_t)B * MG_MAX_RING * MG_FRAME_BYTES));
+    }
+    CK(h, cudaMalloc(&h->tables_dev, sizeof(MgTables)));
+    CK(h, cudaMemcpy(h->tables_dev, mg_tables_host(), sizeof(MgTables), cudaMemcpyHostToDevice));
+    h->S.tables = h->tables_dev;
+    h->S.num_envs = B;
+    CK(h, cudaMalloc(&h->scene_stage_dev, (size_t)B * sizeof(mg_scene)));
+    CK(h, cudaMalloc(&h->ids_stage_dev, (size_t)B * sizeof(int32_t)));
+    h->obs_bytes = (size_t)B * MG_LORES * MG_LORES * 3 * (cfg->n_groups > 0 ? cfg->n_groups : 1);
+    CK(h, cudaMalloc(&h->actions_dev, (size_t)B * sizeof(int32_t)));
+    CK(h, cudaMalloc(&h->obs_dev, h->obs_bytes));
+    CK(h, cudaMalloc(&h->reward_dev, (size_t)B * sizeof(float)));
+    CK(h, cudaMalloc(&h->score_dev, (size_t)B * sizeof(float)));
+    CK(h, cudaMalloc(&h->done_dev, (size_t)B));
+    CK(h, cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CK(h, cudaEventCreate(&h->ev[i]));
+    *out = h;
+    return MG_OK;
+}
+
+extern "C" int mg_destroy(mg_handle *h)
+{
+    if (!h) return MG_OK;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    cudaFree(h->S.dstate); cudaFree(h->S.istate); cudaFree(h->S.scenes); cudaFree(h->S.prims);
+    cudaFree(h->S.n_prims); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
+    cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
+    cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
+    cudaStreamDestroy(h->own_stream);
+    for (int i = 0; i < 4; i++) cudaEventDestroy(h->ev[i]);
+    delete h;
+    return MG_OK;
+}
+
+static int check_launch(mg_handle *h, const char *what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(h, MG_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return MG_OK;
+}
+
+extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream)
+{
+    if (!h || !scenes_host || n < 0 || n > h->cfg.num_envs) return fail(h, MG_ERR_ARG, "mg_set_scenes: bad argument");
+    if (n == 0) return MG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->cfg.device));
+    for (int i = 0; i < n; i++) {
+        if (env_ids_host && (env_ids_host[i] < 0 || env_ids_host[i] >= h->cfg.num_envs))
+            return fail(h, MG_ERR_ARG, "mg_set_scenes: env id out of range");
+        const mg_scene &s = scenes_host[i];
+        if (s.n_blocks < 0 || s.n_blocks > MG_MAX_BLOCKS || s.n_goals < 0 || s.n_goals > MG_MAX_GOALS ||
+            s.task < 0 || s.task >= MG_NUM_TASKS)
+            return fail(h, MG_ERR_ARG, "mg_set_scenes: scene out of range");
+    }
+    CK(h, cudaMemcpyAsync(h->scene_stage_dev, scenes_host, (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
+    if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, env_ids_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    mg_launch_init(h->S, h->scene_stage_dev, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
+    h->launches++;
+    /* the staging buffers are reused by the next call and the host arrays may be pageable */
+    CK(h, cudaStreamSynchronize(st));
+    return check_launch(h, "mg_init_kernel");
+}
+
+static void time_begin(mg_handle *h, int which, cudaStream_t st) { if (h->timing) cudaEventRecord(h->ev[2 * which], st); }
+static void time_end(mg_handle *h, int which, int n_launches, cudaStream_t st)
+{
+    if (!h->timing) return;
+    cudaEventRecord(h->ev[2 * which + 1], st);
+    cudaEventSynchronize(h->ev[2 * which + 1]);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, h->ev[2 * which], h->ev[2 * which + 1]);
+    h->ms[which] += ms;
+    h->timed_launches[which] += n_launches;
+}
+
+extern "C" int mg_step_physics(mg_handle *h, const int32_t *actions_dev, float *reward_dev, uint8_t *done_dev,
+                               float *score_dev, void *stream)
+{
+    if (!h || !actions_dev) return fail(h, MG_ERR_ARG, "mg_step_physics: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->cfg.device));
+    time_begin(h, 0, st);
+    mg_launch_physics(h->S, actions_dev, reward_dev, done_dev, score_dev, st);
+    h->launches++;
+    time_end(h, 0, 1, st);
+    return check_launch(h, "mg_physics_kernel");
+}
+
+/* render every view the observation needs, push into the frame rings, write the stacked observation */
+extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
+{
+    if (!h) return fail(h, MG_ERR_ARG, "mg_step_render: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->cfg.device));
+    int last_view = -1;
+    for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); last_view = v; }
+    time_begin(h, 1, st);
+    int nl = 0;
+    for (int v = 0; v < 2; v++) {
+        if (!h->spec.render_view[v]) continue;
+        bool fuse = h->fused && v == last_view && obs_dev;
+        mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, st);
+        nl++;
+    }
+    time_end(h, 1, nl, st);
+    if (!h->fused && obs_dev && h->spec.n_groups > 0) { mg_launch_compose(h->S, h->spec, h->slots, obs_dev, st); nl++; }
+    mg_launch_clear_fresh(h->S, st); nl++;
+    h->launches += nl;
+    return check_launch(h, "mg_render_kernel");
+}
+
+extern "C" int mg_reset_obs(mg_handle *h, uint8_t *obs_dev, void *stream) { return mg_step_render(h, obs_dev, stream); }
+
+extern "C" int mg_step(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev, uint8_t *done_dev,
+                       float *score_dev, void *stream)
+{
+    int rc = mg_step_physics(h, actions_dev, reward_dev, done_dev, score_dev, stream);
+    if (rc != MG_OK) return rc;
+    return mg_step_render(h, obs_dev, stream);
+}
+
+extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *obs_host, float *reward_host,
+                            uint8_t *done_host, float *score_host)
+{
+    if (!h || !actions_host) return fail(h, MG_ERR_ARG, "mg_step_host: bad argument");
+    const int B = h->cfg.num_envs;
+    cudaStream_t st = h->own_stream;
+    CK(h, cudaSetDevice(h->cfg.device));
+    CK(h, cudaMemcpyAsync(h->actions_dev, actions_host, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    int rc = mg_step(h, h->actions_dev, h->obs_dev, h->reward_dev, h->done_dev, h->score_dev, st);
+    if (rc != MG_OK) return rc;
+    if (obs_host && h->spec.n_groups > 0) CK(h, cudaMemcpyAsync(obs_host, h->obs_dev, h->obs_bytes, cudaMemcpyDeviceToHost, st));
+    if (reward_host) CK(h, cudaMemcpyAsync(reward_host, h->reward_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (done_host) CK(h, cudaMemcpyAsync(done_host, h->done_dev, (size_t)B, cudaMemcpyDeviceToHost, st));
+    if (score_host) CK(h, cudaMemcpyAsync(score_host, h->score_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CK(h, cudaStreamSynchronize(st));
+    return MG_OK;
+}
+
+extern "C" int mg_render(mg_handle *h, int view, int full_res, uint8_t *out_dev, void *stream)
+{
+    if (!h || !out_dev || view < 0 || view > 1) return fail(h, MG_ERR_ARG, "mg_render: bad argument");
+    CK(h, cudaSetDevice(h->cfg.device));
+    mg_launch_render_out(h->S, view, full_res, out_dev, (cudaStream_t)stream);
+    h->launches++;
+    return check_launch(h, "mg_render_kernel");
+}
+
+extern "C" int mg_score(mg_handle *h, float *score_dev, void *stream)
+{
+    if (!h || !score_dev) return fail(h, MG_ERR_ARG, "mg_score: bad argument");
+    CK(h, cudaSetDevice(h->cfg.device));
+    mg_launch_score(h->S, score_dev, 0, (cudaStream_t)stream);
+    h->launches++;
+    return check_launch(h, "mg_score_kernel");
+}
+
+extern "C" int mg_debug_reward(mg_handle *h, float *reward_dev, void *stream)
+{
+    if (!h || !reward_dev) return fail(h, MG_ERR_ARG, "mg_debug_reward: bad argument");
+    CK(h, cudaSetDevice(h->cfg.device));
+    mg_launch_score(h->S, reward_dev, 1, (cudaStream_t)stream);
+    h->launches++;
+    return check_launch(h, "mg_score_kernel");
+}
+
+extern "C" int mg_get_bodies(mg_handle *h, double *out_host)
+{
+    if (!h || !out_host) return fail(h, MG_ERR_ARG, "mg_get_bodies: bad argument");
+    const int B = h->cfg.num_envs;
+    CK(h, cudaSetDevice(h->cfg.device));
+    CK(h, cudaDeviceSynchronize());
+    std::vector<double> poses((size_t)B * MG_POSE_STRIDE);
+    CK(h, cudaMemcpy(poses.data(), h->S.poses, poses.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    for (int e = 0; e < B; e++)
+        for (int b = 0; b < MG_MAX_BODIES; b++)
+            for (int k = 0; k < 6; k++)
+                out_host[((size_t)e * MG_MAX_BODIES + b) * 6 + k] = poses[(size_t)e * MG_POSE_STRIDE + (b + 1) * MG_POSE_NF + k];
+    return MG_OK;
+}
+
+/* checkpoint blob: D_NF doubles, I_NF ints, the scene, the draw list and the frame rings of one env */
+static const size_t BLOB_D = D_NF * sizeof(double);
+static const size_t BLOB_I = I_NF * sizeof(int);
+static const size_t BLOB_SCENE = sizeof(mg_scene);
+static const size_t BLOB_PRIMS = MG_MAX_PRIMS * sizeof(MgPrim) + 8;
+static const size_t BLOB_RING = 2 * MG_MAX_RING * MG_FRAME_BYTES;
+
+extern "C" size_t mg_state_size(const mg_handle *h) { (void)h; return BLOB_D + BLOB_I + BLOB_SCENE + BLOB_PRIMS + BLOB_RING + 16; }
+
+static int state_xfer(mg_handle *h, const int32_t *env_ids_host, int n, unsigned char *blobs, bool set)
+{
+    if (!h || !blobs || n < 0 || n > h->cfg.num_envs) return fail(h, MG_ERR_ARG, "mg_get/set_state: bad argument");
+    if (n == 0) return MG_OK;
+    CK(h, cudaSetDevice(h->cfg.device));
+    CK(h, cudaDeviceSynchronize());
+    const size_t sz = mg_state_size(h);
+    double *dtmp; int *itmp;
+    CK(h, cudaMalloc(&dtmp, (size_t)n * BLOB_D));
+    CK(h, cudaMalloc(&itmp, (size_t)n * BLOB_I));
+    std::vector<int32_t> ids(n);
+    for (int i = 0; i < n; i++) {
+        ids[i] = env_ids_host ? env_ids_host[i] : i;
+        if (ids[i] < 0 || ids[i] >= h->cfg.num_envs) { cudaFree(dtmp); cudaFree(itmp); return fail(h, MG_ERR_ARG, "env id out of range"); }
+    }
+    CK(h, cudaMemcpy(h->ids_stage_dev, ids.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    cudaMemcpyKind dir = set ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+    if (set)
+        for (int i = 0; i < n; i++) {
+            CK(h, cudaMemcpy(dtmp + (size_t)i * D_NF, blobs + i * sz, BLOB_D, dir));
+            CK(h, cudaMemcpy(itmp + (size_t)i * I_NF, blobs + i * sz + BLOB_D, BLOB_I, dir));
+        }
+    mg_launch_state_gather(h->S, h->ids_stage_dev, n, dtmp, itmp, set ? 1 : 0, 0);
+    h->launches++;
+    CK(h, cudaDeviceSynchronize());
+    for (int i = 0; i < n; i++) {
+        unsigned char *b = blobs + i * sz;
+        int e = ids[i];
+        if (!set) {
+            CK(h, cudaMemcpy(b, dtmp + (size_t)i * D_NF, BLOB_D, dir));
+            CK(h, cudaMemcpy(b + BLOB_D, itmp + (size_t)i * I_NF, BLOB_I, dir));
+        }
+        unsigned char *p = b + BLOB_D + BLOB_I;
+        void *dev_scene = h->S.scenes + e, *dev_prims = h->S.prims + (size_t)e * MG_MAX_PRIMS, *dev_np = h->S.n_prims + e;
+        if (set) {
+            CK(h, cudaMemcpy(dev_scene, p, BLOB_SCENE, dir)); p += BLOB_SCENE;
+            CK(h, cudaMemcpy(dev_prims, p, MG_MAX_PRIMS * sizeof(MgPrim), dir)); p += MG_MAX_PRIMS * sizeof(MgPrim);
+            CK(h, cudaMemcpy(dev_np, p, sizeof(int), dir)); p += 8;
+        } else {
+            CK(h, cudaMemcpy(p, dev_scene, BLOB_SCENE, dir)); p += BLOB_SCENE;
+            CK(h, cudaMemcpy(p, dev_prims, MG_MAX_PRIMS * sizeof(MgPrim), dir)); p += MG_MAX_PRIMS * sizeof(MgPrim);
+            CK(h, cudaMemcpy(p, dev_np, sizeof(int), dir)); p += 8;
+        }
+        for (int v = 0; v < 2; v++) {
+            /* frames are stored oldest-first relative to the handle's current slot so a blob is portable */
+            for (int a = 0; a < MG_MAX_RING; a++) {
+                int slot = (h->slots[v] - (MG_MAX_RING - 1 - a)) & (MG_MAX_RING - 1);
+                uint8_t *dev = h->S.ring[v] + ((size_t)e * MG_MAX_RING + slot) * MG_FRAME_BYTES;
+                if (set) CK(h, cudaMemcpy(dev, p, MG_FRAME_BYTES, dir)); else CK(h, cudaMemcpy(p, dev, MG_FRAME_BYTES, dir));
+                p += MG_FRAME_BYTES;
+            }
+        }
+    }
+    cudaFree(dtmp); cudaFree(itmp);
+    return check_launch(h, "mg_state_copy_kernel");
+}
+
+extern "C" int mg_get_state(mg_handle *h, const int32_t *env_ids_host, int n, void *blobs_host)
+{
+    return state_xfer(h, env_ids_host, n, (unsigned char *)blobs_host, false);
+}
+extern "C" int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, const void *blobs_host)
+{
+    return state_xfer(h, env_ids_host, n, (unsigned char *)blobs_host, true);
+}
+
+extern "C" int64_t mg_launch_count(const mg_handle *h) { return h ? h->launches : 0; }
+extern "C" int mg_set_timing(mg_handle *h, int enable) { if (!h) return MG_ERR_ARG; h->timing = enable; return MG_OK; }
+extern "C" double mg_kernel_ms(mg_handle *h, int which, int reset, int64_t *launches_out)
+{
+    if (!h || which < 0 || which > 1) return 0.0;
+    double ms = h->ms[which];
+    if (launches_out) *launches_out = h->timed_launches[which];
+    if (reset) { h->ms[which] = 0; h->timed_launches[which] = 0; }
+    return ms;
+}
+
+/* ------------------------------------------------------------------ host-side placement predicate */
+
+namespace {
+struct HostShape { WShape s; int ent; };   /* ent: 0 walls, 1 robot, 2+i block i, 100+i goal i */
+
+vec2 rot_of(double a) { return V(cos(a), sin(a)); }
+
+int entity_shapes(const MgTables *T, const mg_scene *sc, int kind, int idx, HostShape *out)
+{
+    int n = 0;
+    if (kind == MG_ENT_ROBOT) {
+        const double *r = sc->robot[MG_RB_ROBOT];
+        wshape_from_tpl(T, MG_TPL_CIRCLE_ROBOT, V(r[0], r[1]), rot_of(r[2]), &out[n].s); out[n++].ent = 1;
+        for (int k = 0; k < 2; k++)
+            for (int part = 0; part < 2; part++) {
+                const double *f = sc->robot[MG_RB_FINGER_L + k];
+                wshape_from_tpl(T, MG_TPL_FINGER0 + k * 2 + part, V(f[0], f[1]), rot_of(f[2]), &out[n].s); out[n++].ent = 1;
+            }
+    } else if (kind == MG_ENT_BLOCK) {
+        const mg_block *b = &sc->blocks[idx];
+        vec2 p = V(b->x, b->y), rot = rot_of(b->angle);
+        int ent = 2 + idx;
+        switch (b->type) {
+        case MG_SQUARE: wshape_from_tpl(T, MG_TPL_SQUARE, p, rot, &out[n].s); out[n++].ent = ent; break;
+        case MG_CIRCLE: wshape_from_tpl(T, MG_TPL_CIRCLE_BLOCK, p, rot, &out[n].s); out[n++].ent = ent; break;
+        case MG_STAR:
+            for (int k = 0; k < MG_STAR_PIECES; k++) { wshape_from_tpl(T, MG_TPL_STAR0 + k, p, rot, &out[n].s); out[n++].ent = ent; }
+            break;
+        default: wshape_from_tpl(T, MG_TPL_PENT, p, rot, &out[n].s); out[n++].ent = ent; break;
+        }
+    } else {
+        const mg_goal *g = &sc->goals[idx];
+        double hw = g->w / 2, hh = g->h / 2;
+        vec2 lv[4] = { V(hw, -hh), V(hw, hh), V(-hw, hh), V(-hw, -hh) };
+        WShape *s = &out[n].s;
+        s->kind = MG_SHAPE_POLY; s->n = 4; s->r = 0.0;
+        for (int i = 0; i < 4; i++) {
+            vec2 a = lv[(i + 3) % 4], b = lv[i];
+            double dx = b.x - a.x, dy = b.y - a.y, nx = dy, ny = -dx;
+            double inv = 1.0 / (sqrt(nx * nx + ny * ny) + MG_DBL_MIN);
+            s->v[i] = V(b.x + g->cx, b.y + g->cy);
+            s->nrm[i] = V(nx * inv, ny * inv);
+        }
+        out[n++].ent = 100 + idx;
+    }
+    return n;
+}
+
+bool touches(const WShape *a, const WShape *b)
+{
+    Manifold m;
+    return (a->kind <= b->kind ? collide_shapes(a, b, &m) : collide_shapes(b, a, &m)) > 0;
+}
+} // namespace
+
+extern "C" int mg_host_entity_overlaps(const mg_scene *scene, int kind, int idx, int robot_active,
+                                       uint32_t block_mask, uint32_t goal_mask)
+{
+    const MgTables *T = mg_tables_host();
+    HostShape mine[8], other[8];
+    int nm = entity_shapes(T, scene, kind, idx, mine);
+    for (int i = 0; i < nm; i++) {
+        /* arena walls are always collidable */
+        for (int w = 0; w < 4; w++) {
+            WShape ws;
+            wshape_from_tpl(T, MG_TPL_WALL0 + w, V(0, 0), V(1, 0), &ws);
+            if (touches(&mine[i].s, &ws)) return 1;
+        }
+    }
+    for (int pass = 0; pass < 3; pass++) {
+        int count = pass == 0 ? 1 : (pass == 1 ? scene->n_blocks : scene->n_goals);
+        for (int j = 0; j < count; j++) {
+            int okind = pass == 0 ? MG_ENT_ROBOT : (pass == 1 ? MG_ENT_BLOCK : MG_ENT_GOAL);
+            if (okind == kind && (kind == MG_ENT_ROBOT || j == idx)) continue;
+            if (pass == 0 && !robot_active) continue;
+            if (pass == 1 && !(block_mask >> j & 1)) continue;
+            if (pass == 2 && !(goal_mask >> j & 1)) continue;
+            int no = entity_shapes(T, scene, okind, j, other);
+            for (int a = 0; a < nm; a++)
+                for (int b = 0; b < no; b++)
+                    if (touches(&mine[a].s, &other[b].s)) return 1;
+        }
+    }
+    return 0;
+}

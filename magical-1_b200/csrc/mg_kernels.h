@@ -19,9 +19,9 @@ struct MgDeviceState {
     int *n_prims;            /* [B] */
     double *poses;           /* [B][MG_NB][MG_POSE_NF] exported after every reset / step */
     const MgTables *tables;  /* device copy */
-    /* frame stacks: ring[view] = u8 [B][MG_MAX_RING][96][96][3]; head[env] = slot of the newest frame */
+    /* frame stacks: ring[view] = u8 [B][MG_MAX_RING][96][96][3]; the newest slot is the same for all envs
+     * (every env pushes one frame per step) and is tracked on the host */
     uint8_t *ring[2];
-    int *ring_head;          /* [B][2] */
 };
 
 struct MgObsSpec {
@@ -35,10 +35,12 @@ struct MgObsSpec {
 void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st);
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st);
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);
-/* render `view` of every env into the frame stacks (push) */
-void mg_launch_render_push(const MgDeviceState &S, int view, cudaStream_t st);
-/* compose the stacked observation from the rings */
-void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, uint8_t *obs, cudaStream_t st);
+/* render `view` of every env and push the 96x96 frame into ring slot `slot`; when `fused` is given the
+ * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v) */
+void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
+                           uint8_t *obs, cudaStream_t st);
+/* compose the stacked observation from the rings (any view mix, HWC or CHW) */
+void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int *slots, uint8_t *obs, cudaStream_t st);
 /* clear the per-env "fresh" flag after all views were pushed */
 void mg_launch_clear_fresh(const MgDeviceState &S, cudaStream_t st);
 /* stand-alone render of one view: full_res ? [B,384,384,3] : [B,96,96,3] */

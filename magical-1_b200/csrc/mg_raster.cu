@@ -1,0 +1,559 @@
+/*
+ * mg_raster.cu -- fused raster -> 4x area downsample -> frame-stack kernel.
+ *
+ * Stands in for BaseEnv.render('rgb_array') (magical/base_env.py:324-343), Viewer.render
+ * and Poly._render / draw_outline (magical/render.py:212-287, 385-395) on a pygame 1.9.6
+ * software surface, ResizeDictObservation's cv2.resize(INTER_AREA) at exactly 4x
+ * (magical/benchmarks/__init__.py:150-190) and FlattenFrameStack / EagerDictFrameStack
+ * (magical/benchmarks/__init__.py:51-147).
+ *
+ * Work decomposition: one WARP renders one 32-row band of one (env, view) into a
+ * palette-index buffer in shared memory (painter's algorithm: later primitives overwrite
+ * earlier ones, exactly like drawing on the surface), then reduces the band to 8 rows of
+ * the 96x96 frame with round-half-even of the 16-sample sum, stores them into the env's
+ * frame ring with 16-byte stores and, when the observation is a stack of frames of this
+ * view, also writes the band of the stacked uint8 HWC observation.  Bands never share
+ * state, so there is no CTA-level synchronisation after the palette load.
+ *
+ * pygame rules restated (draw.c of pygame 1.9.6): polygon vertices truncated to int,
+ * scanline fill with integer-division crossings, width-2 / width-4 lines as offset copies
+ * of an integer DDA line after Cohen-Sutherland clipping with a float slope.
+ */
+#include <cuda_runtime.h>
+#include "mg_state.cuh"
+#include "mg_kernels.h"
+
+#define RES MG_RES
+#define BAND_ROWS 32
+#define N_BANDS (RES / BAND_ROWS)
+#define ROW_STRIDE 388                       /* 97 words: lane-per-row word stores are bank-conflict free */
+#define LO_ROWS (BAND_ROWS / 4)
+#define LO_BAND_BYTES (LO_ROWS * MG_LORES * 3)   /* 2304 */
+#define WARPS_PER_CTA 4
+#define FULL 0xffffffffu
+
+struct aff { double a, b, tx, c, d, ty; };   /* 3x3 homogeneous matrix, last row 0 0 1 */
+
+/* numpy `A @ B` on such matrices: every entry is (p*q + r*s) + t*u */
+__device__ __forceinline__ aff aff_mul(aff A, aff B)
+{
+    aff C;
+    C.a = (A.a * B.a + A.b * B.c) + A.tx * 0.0;
+    C.b = (A.a * B.b + A.b * B.d) + A.tx * 0.0;
+    C.tx = (A.a * B.tx + A.b * B.ty) + A.tx * 1.0;
+    C.c = (A.c * B.a + A.d * B.c) + A.ty * 0.0;
+    C.d = (A.c * B.b + A.d * B.d) + A.ty * 0.0;
+    C.ty = (A.c * B.tx + A.d * B.ty) + A.ty * 1.0;
+    return C;
+}
+/* Transform(translation, rotation) with unit scale (render.py:87-97): T @ R @ S is exactly this */
+__device__ __forceinline__ aff aff_tr(double tx, double ty, double cs, double sn)
+{
+    aff X = { cs, -sn, tx, sn, cs, ty };
+    return X;
+}
+__device__ __forceinline__ aff aff_scale(double sx, double sy)
+{
+    aff X = { sx, 0.0, 0.0, 0.0, sy, 0.0 };
+    return X;
+}
+/* Viewer.pygame_transform = T(0, H) @ S(1, -1) (render.py:329-330) */
+__device__ __forceinline__ aff pygame_transform()
+{
+    return aff_mul(aff_tr(0.0, (double)RES, 1.0, 0.0), aff_scale(1.0, -1.0));
+}
+/* BaseEnv._use_allo_cam + Viewer.set_bounds (base_env.py:318-322, render.py:339-347) */
+__device__ aff allo_camera()
+{
+    const double zoom = 1.02;   /* style.ARENA_ZOOM_OUT */
+    double left = -1 * zoom, right = 1 * zoom, bottom = -1 * zoom, top = 1 * zoom;
+    double sx = RES / (right - left), sy = RES / (top - bottom);
+    aff cam = aff_mul(aff_mul(aff_tr(-left * sx, -bottom * sy, 1.0, 0.0), aff_tr(0.0, 0.0, 1.0, 0.0)), aff_scale(sx, sy));
+    return aff_mul(pygame_transform(), cam);
+}
+/* BaseEnv._use_ego_cam + Viewer.set_cam_follow + ego_cam_matrix (base_env.py:309-316, render.py:290-304, 349-371) */
+__device__ aff ego_camera(double cx, double cy, double cs, double sn)
+{
+    const double zoom = 1.02;
+    double world_h = 2 * zoom, world_w = 2 * zoom;
+    double sx = RES / world_w, sy = RES / world_h;
+    aff scale = aff_scale(sx, sy);
+    aff tr1 = aff_tr(world_w * 0.5, world_h * 0.15, 1.0, 0.0);
+    aff rot = aff_tr(0.0, 0.0, cs, -sn);         /* rotation by -theta: cos(-t) = cos t, sin(-t) = -sin t */
+    aff tr2 = aff_tr(-cx, -cy, 1.0, 0.0);
+    aff m = aff_mul(rot, tr2);
+    m = aff_mul(tr1, m);
+    m = aff_mul(scale, m);
+    return aff_mul(pygame_transform(), m);
+}
+
+struct WarpSmem {
+    uint8_t buf[BAND_ROWS * ROW_STRIDE];     /* palette indices of the band */
+    int vx[MG_CIRCLE_RES + 4], vy[MG_CIRCLE_RES + 4];
+    double fx[4], fy[4];                     /* float vertices (dashed outlines only) */
+    uint8_t lo[LO_BAND_BYTES];               /* downsampled band, HWC */
+};
+
+/* ---------------------------------------------------------------- lines (pygame draw.c) */
+
+/* clipline: Cohen-Sutherland against [0, RES-1]^2 with a float slope */
+__device__ __forceinline__ int clip_encode(int x, int y)
+{
+    int code = 0;
+    if (x < 0) code |= 1;
+    if (x > RES - 1) code |= 2;
+    if (y < 0) code |= 8;
+    if (y > RES - 1) code |= 4;
+    return code;
+}
+__device__ bool clipline(int &x1, int &y1, int &x2, int &y2)
+{
+    const int left = 0, right = RES - 1, top = 0, bottom = RES - 1;
+    while (true) {
+        int code1 = clip_encode(x1, y1), code2 = clip_encode(x2, y2);
+        if (!(code1 | code2)) return true;
+        if (code1 & code2) return false;
+        if (!code1) {
+            int t = x2; x2 = x1; x1 = t;
+            t = y2; y2 = y1; y1 = t;
+            t = code2; code2 = code1; code1 = t;
+        }
+        float m = 1.0f;
+        if (x2 != x1) m = __fdiv_rn((float)(y2 - y1), (float)(x2 - x1));
+        if (code1 & 1) { y1 += (int)__fmul_rn((float)(left - x1), m); x1 = left; }
+        else if (code1 & 2) { y1 += (int)__fmul_rn((float)(right - x1), m); x1 = right; }
+        else if (code1 & 4) { if (x2 != x1) x1 += (int)__fdiv_rn((float)(bottom - y1), m); y1 = bottom; }
+        else if (code1 & 8) { if (x2 != x1) x1 += (int)__fdiv_rn((float)(top - y1), m); y1 = top; }
+    }
+}
+
+/* One clipped line = pixels k = 0..len-1 of pygame's integer DDA (drawline / drawhorzline /
+ * drawvertline produce the same set): the major axis advances by one per pixel, the minor
+ * axis by floor(k * minor_len / major_len). */
+struct Line { int x1, y1, sx, sy, dxp, dyp, len; bool xmajor; };
+
+__device__ __forceinline__ bool line_setup(int x1, int y1, int x2, int y2, Line &L)
+{
+    if (!clipline(x1, y1, x2, y2)) return false;
+    if (y1 == y2 && x1 > x2) { int t = x1; x1 = x2; x2 = t; }   /* drawhorzline / drawvertline order: same pixels */
+    int dx = x2 - x1, dy = y2 - y1;
+    L.sx = dx < 0 ? -1 : 1; L.sy = dy < 0 ? -1 : 1;
+    L.dxp = L.sx * dx + 1; L.dyp = L.sy * dy + 1;
+    L.x1 = x1; L.y1 = y1;
+    L.xmajor = !(L.dxp < L.dyp);
+    L.len = L.xmajor ? L.dxp : L.dyp;
+    return true;
+}
+__device__ __forceinline__ void line_pixel(const Line &L, int k, int &x, int &y)
+{
+    if (L.xmajor) { x = L.x1 + L.sx * k; y = L.y1 + L.sy * ((k * L.dyp) / L.dxp); }
+    else { y = L.y1 + L.sy * k; x = L.x1 + L.sx * ((k * L.dxp) / L.dyp); }
+}
+__device__ __forceinline__ void put_px(uint8_t *buf, int y0, int x, int y, uint8_t c)
+{
+    unsigned r = (unsigned)(y - y0);
+    if (r < BAND_ROWS) buf[r * ROW_STRIDE + x] = c;
+}
+
+/* offsets of clip_and_draw_line_width: width 2 -> 0,+1; width 4 -> 0,+1,-1,+2 */
+__device__ __forceinline__ int width_offset(int copy) { return copy == 0 ? 0 : (copy == 1 ? 1 : (copy == 2 ? -1 : 2)); }
+
+/* all pixels of one line copy, pixels spread over the lanes of the warp */
+__device__ void draw_line_warp(uint8_t *buf, int y0, int lane, int x1, int y1, int x2, int y2, uint8_t c)
+{
+    if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
+    Line L;
+    if (!line_setup(x1, y1, x2, y2, L)) return;
+    for (int k = lane; k < L.len; k += 32) {
+        int x, y;
+        line_pixel(L, k, x, y);
+        put_px(buf, y0, x, y, c);
+    }
+}
+/* all pixels of one line copy, drawn by the calling lane alone */
+__device__ void draw_line_lane(uint8_t *buf, int y0, int x1, int y1, int x2, int y2, uint8_t c)
+{
+    if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
+    Line L;
+    if (!line_setup(x1, y1, x2, y2, L)) return;
+    for (int k = 0; k < L.len; k++) {
+        int x, y;
+        line_pixel(L, k, x, y);
+        put_px(buf, y0, x, y, c);
+    }
+}
+
+/* np.arange(start, stop, step)[i] for doubles (numpy fills start, start+step, then start + i*delta) */
+__device__ __forceinline__ int arange_len(double start, double stop, double step)
+{
+    double len_f = ceil((stop - start) / step);
+    return len_f <= 0 ? 0 : (int)len_f;
+}
+__device__ __forceinline__ double arange_at(double start, double step, int i)
+{
+    if (i == 0) return start;
+    if (i == 1) return start + step;
+    double delta = (start + step) - start;
+    return start + i * delta;
+}
+
+/* ---------------------------------------------------------------- one primitive (render.Poly) */
+
+/* Poly.draw_outline(dashed=True) for one edge (render.py:232-255): dash d joins arange point 2d+1 to 2d */
+__device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, double y1, double x2, double y2, uint8_t c)
+{
+    const double dl = 10;
+    int n;
+    double sx_ = 0, sy_ = 0;   /* steps; 0 = constant coordinate */
+    if (x1 == x2) {
+        sy_ = y1 < y2 ? dl : -dl;
+        n = arange_len(y1, y2, sy_);
+    } else if (y1 == y2) {
+        sx_ = x1 < x2 ? dl : -dl;
+        n = arange_len(x1, x2, sx_);
+    } else {
+        double a = fabs(x2 - x1), b = fabs(y2 - y1);
+        double cc = rint(sqrt(a * a + b * b));
+        double dx = dl * a / cc, dy = dl * b / cc;
+        sx_ = x1 < x2 ? dx : -dx;
+        sy_ = y1 < y2 ? dy : -dy;
+        int nx = arange_len(x1, x2, sx_), ny = arange_len(y1, y2, sy_);
+        n = nx < ny ? nx : ny;
+    }
+    int n_dash = n / 2;
+    /* lane = (dash, copy) */
+    for (int job = lane; job < n_dash * 4; job += 32) {
+        int d = job >> 2, copy = job & 3;
+        double xa = sx_ != 0 ? arange_at(x1, sx_, 2 * d + 1) : x1, ya = sy_ != 0 ? arange_at(y1, sy_, 2 * d + 1) : y1;
+        double xb = sx_ != 0 ? arange_at(x1, sx_, 2 * d) : x1, yb = sy_ != 0 ? arange_at(y1, sy_, 2 * d) : y1;
+        int px1 = (int)rint(xa), py1 = (int)rint(ya), px2 = (int)rint(xb), py2 = (int)rint(yb);
+        int off = width_offset(copy);
+        if (abs(px1 - px2) > abs(py1 - py2)) { py1 += off; py2 += off; } else { px1 += off; px2 += off; }
+        draw_line_lane(buf, y0, px1, py1, px2, py2, c);
+    }
+}
+
+/* pygame.draw.polygon fill of rows [y0, y0+32): lane r owns row y0 + r */
+__device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
+{
+    int y = y0 + lane;
+    if (y < miny || y > maxy) return;
+    int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
+    if (miny == maxy) {
+        /* polygon one pixel high: span = x extent */
+        for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
+        cnt = 2;
+    } else {
+        for (int i = 0; i < n; i++) {
+            int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
+            int x1, y1, x2, y2;
+            if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
+            else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
+            else continue;
+            if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
+                int x = (y - y1) * (x2 - x1) / (y2 - y1) + x1;
+                lo = min(lo, x); hi = max(hi, x); cnt++;
+            }
+        }
+    }
+    if (cnt < 2) return;
+    if (hi < 0 || lo > RES - 1) return;
+    lo = max(lo, 0); hi = min(hi, RES - 1);
+    uint8_t *row = W->buf + lane * ROW_STRIDE;
+    uint32_t c4 = c * 0x01010101u;
+    int x = lo;
+    while (x <= hi && (x & 3)) row[x++] = c;
+    for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
+    for (; x <= hi; x++) row[x] = c;
+}
+
+__device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3)
+{
+    /* 16 palette ids -> per-channel sums -> round-half-even(sum / 16), packed r | g<<8 | b<<16 */
+    uint32_t rs = 0, gs = 0, bs = 0;
+    uint32_t ws[4] = { w0, w1, w2, w3 };
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            uint32_t p = pal[(ws[i] >> (8 * j)) & 31];
+            rs += p & 255; gs += (p >> 8) & 255; bs += (p >> 16) & 255;
+        }
+    uint32_t out = 0;
+    uint32_t s[3] = { rs, gs, bs };
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        uint32_t q = s[k] >> 4, r = s[k] & 15;
+        if (r > 8 || (r == 8 && (q & 1))) q++;
+        out |= q << (8 * k);
+    }
+    return out;
+}
+
+struct RenderArgs {
+    int view;
+    int mode;            /* 0: push into the frame ring (+ optional fused stack); 1: lo-res out; 2: full-res out */
+    uint8_t *out;        /* mode 1: [B,96,96,3]; mode 2: [B,384,384,3] */
+    int slot;            /* ring slot that receives the new frame (mode 0) */
+    /* fused stack: obs[B,96,96,3*n_groups]; group g = frame of view gview[g] in ring slot gslot[g] */
+    uint8_t *obs;
+    int n_groups;
+    int gview[MG_MAX_GROUPS], gslot[MG_MAX_GROUPS], gage[MG_MAX_GROUPS];
+};
+
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceState S, RenderArgs A)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t pal[32];
+    const MgTables *T = S.tables;
+    if (threadIdx.x < 32) {
+        const uint8_t *p = T->pal[threadIdx.x];
+        pal[threadIdx.x] = p[0] | (p[1] << 8) | (p[2] << 16);
+    }
+    __syncthreads();
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
+    int env = (int)(item / N_BANDS), band = (int)(item % N_BANDS);
+    if (env >= S.num_envs) return;
+    WarpSmem *W = (WarpSmem *)smem_raw + warp;
+    const int y0 = band * BAND_ROWS;
+    const double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
+    const double *rp = pose + MG_BODY_ROBOT * MG_POSE_NF;
+
+    /* Viewer._clear: background */
+    for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 4; i += 32) ((uint32_t *)W->buf)[i] = MG_PAL_BG * 0x01010101u;
+    aff cam = A.view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
+    aff cam_robot = aff_mul(cam, aff_tr(rp[0], rp[1], rp[6], rp[7]));
+    __syncwarp();
+
+    const MgPrim *prims = S.prims + (size_t)env * MG_MAX_PRIMS;
+    int np = S.n_prims[env];
+    for (int pi = 0; pi < np; pi++) {
+        MgPrim P = prims[pi];
+        aff M;
+        const vec2 *lv = T->dl_pool + T->dl_off[P.dl];
+        int n = T->dl_n[P.dl];
+        double gw = 0, gh = 0;
+        switch (P.chain) {
+        case MG_CHAIN_CAM: M = cam; break;
+        case MG_CHAIN_BODY: {
+            const double *b = pose + P.body * MG_POSE_NF;
+            M = P.body == MG_BODY_ROBOT ? cam_robot : aff_mul(cam, aff_tr(b[0], b[1], b[6], b[7]));
+            break;
+        }
+        case MG_CHAIN_EYE:
+        case MG_CHAIN_PUPIL: {
+            const double radius = 0.2;
+            double x_sign = P.aux == 0 ? -1.0 : 1.0;
+            M = aff_mul(cam_robot, aff_tr(x_sign * 0.4 * radius, 0.3 * radius, 1.0, 0.0));
+            if (P.chain == MG_CHAIN_PUPIL) {
+                double rel = pose[P.body * MG_POSE_NF + 2] - rp[2];   /* pupil.angle - robot.angle, entities.py:489-491 */
+                double sn, cs;
+                sincos(rel, &sn, &cs);
+                M = aff_mul(M, aff_tr(0.0, 0.0, cs, sn));
+                M = aff_mul(M, aff_tr(0.0, radius * 0.07, 1.0, 0.0));
+            }
+            break;
+        }
+        default: { /* MG_CHAIN_GOAL */
+            const mg_goal *g = &S.scenes[env].goals[P.aux];
+            M = aff_mul(cam, aff_tr(g->cx, g->cy, 1.0, 0.0));
+            gw = g->w; gh = g->h;
+            break;
+        }
+        }
+        /* transform + truncate vertices (stack.apply_current_matrix, then pygame's int conversion) */
+        int miny = 0x7fffffff, maxy = -0x7fffffff - 1;
+        for (int i = lane; i < n; i += 32) {
+            double x, y;
+            if (P.chain == MG_CHAIN_GOAL) {
+                double rw = gw / 2, rh = gh / 2;
+                x = (i == 0 || i == 3) ? -rw : rw;
+                y = (i < 2) ? rh : -rh;
+            } else { x = lv[i].x; y = lv[i].y; }
+            double fx = (M.a * x + M.b * y) + M.tx;
+            double fy = (M.c * x + M.d * y) + M.ty;
+            int ix = (int)fx, iy = (int)fy;
+            W->vx[i] = ix; W->vy[i] = iy;
+            if (n <= 4) { W->fx[i] = fx; W->fy[i] = fy; }
+            miny = min(miny, iy); maxy = max(maxy, iy);
+        }
+        miny = __reduce_min_sync(FULL, miny);
+        maxy = __reduce_max_sync(FULL, maxy);
+        __syncwarp();
+        if (lane == 0) { W->vx[n] = W->vx[0]; W->vy[n] = W->vy[0]; }
+        __syncwarp();
+        /* outlines reach at most 2 pixels beyond the vertex rows */
+        if (maxy + 2 >= y0 && miny - 2 < y0 + BAND_ROWS) {
+            fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
+            __syncwarp();
+            if (P.mode == 1) {
+                /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
+                if (n <= 8) {
+                    for (int i = 0; i < n; i++)
+                        for (int copy = 0; copy < 2; copy++) {
+                            int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
+                            if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
+                            draw_line_warp(W->buf, y0, lane, x1, y1, x2, y2, P.outline);
+                        }
+                } else {
+                    for (int job = lane; job < 2 * n; job += 32) {
+                        int i = job >> 1, copy = job & 1;
+                        int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
+                        if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
+                        draw_line_lane(W->buf, y0, x1, y1, x2, y2, P.outline);
+                    }
+                }
+            } else if (P.mode == 2) {
+                for (int i = 0; i < n; i++) {
+                    int j = (i + 1) % n;
+                    draw_dashed_edge(W->buf, y0, lane, W->fx[i], W->fy[i], W->fx[j], W->fy[j], P.outline);
+                }
+            }
+        }
+        __syncwarp();
+    }
+
+    if (A.mode == 2) {
+        /* full resolution: surfarray.array3d(...).swapaxes(0, 1) -> u8 [384, 384, 3] (render.py:394-395) */
+        uint32_t *dst = (uint32_t *)(A.out + ((size_t)env * RES + y0) * RES * 3);
+        for (int g = lane; g < BAND_ROWS * (RES / 4); g += 32) {
+            int r = g / (RES / 4), q = g % (RES / 4);
+            uint32_t w = *(const uint32_t *)(W->buf + r * ROW_STRIDE + q * 4);
+            uint32_t c0 = pal[w & 31], c1 = pal[(w >> 8) & 31], c2 = pal[(w >> 16) & 31], c3 = pal[(w >> 24) & 31];
+            uint32_t *o = dst + (size_t)g * 3;
+            o[0] = c0 | (c1 << 24);
+            o[1] = (c1 >> 8) | (c2 << 16);
+            o[2] = (c2 >> 16) | (c3 << 8);
+        }
+        return;
+    }
+
+    /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block */
+    for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {
+        int oy = o / MG_LORES, ox = o % MG_LORES;
+        const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
+        uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
+        uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
+        uint32_t rgb;
+        if (w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u) rgb = pal[w0 & 31];
+        else rgb = pal_sum16(pal, w0, w1, w2, w3);
+        uint8_t *d = W->lo + o * 3;
+        d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+    }
+    __syncwarp();
+
+    const size_t band_off = (size_t)band * LO_BAND_BYTES;
+    if (A.mode == 1) {
+        uint4 *dst = (uint4 *)(A.out + (size_t)env * MG_FRAME_BYTES + band_off);
+        for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
+        return;
+    }
+
+    /* mode 0: push into the frame ring.  A freshly reset env fills every slot with its first
+     * frame (FlattenFrameStack.reset / EagerDictFrameStack.reset, benchmarks/__init__.py:66-74, 139-147) */
+    const bool fresh = S.istate[mg_field_index(env, I_NF, I_FRESH)] != 0;
+    uint8_t *ring = S.ring[A.view] + (size_t)env * MG_MAX_RING * MG_FRAME_BYTES;
+    for (int s = 0; s < MG_MAX_RING; s++) {
+        if (!fresh && s != A.slot) continue;
+        uint4 *dst = (uint4 *)(ring + (size_t)s * MG_FRAME_BYTES + band_off);
+        for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
+    }
+    if (!A.obs) return;
+
+    /* fused frame stack: obs[env, 8 rows of this band, 96, 3 * n_groups], channel group g taken from
+     * the ring slot the host computed for (view, age).  Frames of this view that are being written
+     * by this very launch (age 0, or any age of a fresh env) come from shared memory. */
+    const int G = A.n_groups, C = 3 * G;
+    uint32_t *obs_w = (uint32_t *)(A.obs + ((size_t)env * MG_LORES * MG_LORES + (size_t)band * LO_ROWS * MG_LORES) * C);
+    for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {      /* q = group of 4 consecutive pixels */
+        uint32_t src[MG_MAX_GROUPS][3];
+        for (int g = 0; g < G; g++) {
+            const uint32_t *p;
+            if (A.gview[g] == A.view && (A.gage[g] == 0 || fresh)) p = (const uint32_t *)W->lo + q * 3;
+            else p = (const uint32_t *)(S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES + band_off) + q * 3;
+            src[g][0] = p[0]; src[g][1] = p[1]; src[g][2] = p[2];
+        }
+        /* output byte (pixel px, channel ch) = byte (3 * px + ch % 3) of group ch / 3 */
+        for (int w = 0; w < 3 * G; w++) {
+            uint32_t word = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                int byte = w * 4 + k;
+                int px = byte / C, ch = byte % C;
+                int g = ch / 3, sb = 3 * px + ch % 3;
+                word |= ((src[g][sb >> 2] >> (8 * (sb & 3))) & 255u) << (8 * k);
+            }
+            obs_w[(size_t)q * 3 * G + w] = word;
+        }
+    }
+}
+
+/* generic stack composer: any mix of views, HWC or CHW (LoResStack, LoRes3EA, LoResCHW*) */
+__global__ void mg_compose_kernel(MgDeviceState S, MgObsSpec spec, int slot0, int slot1, uint8_t *obs)
+{
+    int env = blockIdx.x;
+    const int G = spec.n_groups, C = 3 * G;
+    uint8_t *o = obs + (size_t)env * MG_LORES * MG_LORES * C;
+    for (int idx = threadIdx.x; idx < MG_LORES * MG_LORES * C; idx += blockDim.x) {
+        int pix, ch;
+        if (spec.chw) { ch = idx / (MG_LORES * MG_LORES); pix = idx % (MG_LORES * MG_LORES); }
+        else { pix = idx / C; ch = idx % C; }
+        int g = ch / 3, v = spec.view[g];
+        int slot = ((v == 0 ? slot0 : slot1) - spec.age[g]) & (MG_MAX_RING - 1);
+        o[idx] = S.ring[v][((size_t)env * MG_MAX_RING + slot) * MG_FRAME_BYTES + pix * 3 + ch % 3];
+    }
+}
+
+__global__ void mg_clear_fresh_kernel(MgDeviceState S)
+{
+    int env = blockIdx.x * blockDim.x + threadIdx.x;
+    if (env < S.num_envs) S.istate[mg_field_index(env, I_NF, I_FRESH)] = 0;
+}
+
+static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st)
+{
+    static bool attr_set = false;
+    size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA;
+    if (!attr_set) {
+        cudaFuncSetAttribute(mg_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+    }
+    long long items = (long long)S.num_envs * N_BANDS;
+    int grid = (int)((items + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    mg_render_kernel<<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A);
+}
+
+void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
+                           uint8_t *obs, cudaStream_t st)
+{
+    RenderArgs A;
+    memset(&A, 0, sizeof(A));
+    A.view = view; A.mode = 0; A.slot = slot;
+    if (fused && obs) {
+        A.obs = obs; A.n_groups = fused->n_groups;
+        for (int g = 0; g < fused->n_groups; g++) {
+            A.gview[g] = fused->view[g]; A.gage[g] = fused->age[g];
+            A.gslot[g] = (slots[fused->view[g]] - fused->age[g]) & (MG_MAX_RING - 1);
+        }
+    }
+    launch_render(S, A, st);
+}
+
+void mg_launch_render_out(const MgDeviceState &S, int view, int full_res, uint8_t *out, cudaStream_t st)
+{
+    RenderArgs A;
+    memset(&A, 0, sizeof(A));
+    A.view = view; A.mode = full_res ? 2 : 1; A.out = out;
+    launch_render(S, A, st);
+}
+
+void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int *slots, uint8_t *obs, cudaStream_t st)
+{
+    mg_compose_kernel<<<S.num_envs, 256, 0, st>>>(S, spec, slots[0], slots[1], obs);
+}
+
+void mg_launch_clear_fresh(const MgDeviceState &S, cudaStream_t st)
+{
+    mg_clear_fresh_kernel<<<(S.num_envs + 127) / 128, 128, 0, st>>>(S);
+}
