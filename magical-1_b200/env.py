@@ -1,0 +1,266 @@
+"""Batched MAGICAL env on one B200 and its single-env gym-style view.
+
+Mirrors the reference's env protocol for the hot path:
+  BaseEnv.reset / step / render / seed / close      magical/base_env.py:134-141, 190-356
+  preprocessor wrapper stacks (LoRes*)               magical/benchmarks/__init__.py:51-306
+All simulation, rendering, resizing and frame stacking happens in libmagical_b200.so; this
+module samples resets on the host (tasks.py), owns the torch tensors that receive the results
+and keeps the per-env episode counters.  torch is used for device memory and streams only.
+"""
+import collections
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+from . import tasks
+
+# preprocessor -> list of (view, age) channel groups of the stacked tensor, oldest first
+# (FlattenFrameStack: allo block before ego block, benchmarks/__init__.py:122-129, 269-306)
+_E, _A = L.VIEW_EGO, L.VIEW_ALLO
+PREPROC_SPECS = collections.OrderedDict([
+    ('LoRes3EA', dict(groups=[(_A, 0), (_E, 2), (_E, 1), (_E, 0)], kind='flat', chw=False)),
+    ('LoRes4E', dict(groups=[(_E, 3), (_E, 2), (_E, 1), (_E, 0)], kind='flat', chw=False)),
+    ('LoRes4A', dict(groups=[(_A, 3), (_A, 2), (_A, 1), (_A, 0)], kind='flat', chw=False)),
+    ('LoResStack', dict(groups=[(_A, 3), (_A, 2), (_A, 1), (_A, 0), (_E, 3), (_E, 2), (_E, 1), (_E, 0)],
+                        kind='stack', chw=False)),
+    ('LoResCHW4E', dict(groups=[(_E, 3), (_E, 2), (_E, 1), (_E, 0)], kind='flat', chw=True)),
+    # registered with allo_frames=0, ego_frames=4 in the reference too (benchmarks/__init__.py:301-306)
+    ('LoResCHW4A', dict(groups=[(_E, 3), (_E, 2), (_E, 1), (_E, 0)], kind='flat', chw=True)),
+])
+
+
+def _torch():
+    import torch
+    return torch
+
+
+class BatchedMagicalEnv:
+    """`num_envs` independent copies of one registered env id, stepped together on one GPU.
+
+    reset() -> obs dict of uint8 torch tensors on the device
+    step(actions[int, B]) -> (obs, reward f32[B], done bool[B], {'eval_score': f32[B]})
+    Envs that reach their horizon are reset on the host (their own RandomState, reference draw
+    order) before the step's render, so the returned observation of a finished env is the first
+    observation of its next episode; reward/done/eval_score still belong to the finished one.
+    """
+
+    def __init__(self, entry_point, env_kwargs, max_episode_steps, preproc=None, num_envs=1, device=0,
+                 seed=None, obs_keys=None, auto_reset=True, env_ids=None):
+        torch = _torch()
+        if not torch.cuda.is_available():
+            raise RuntimeError('magical_b200 needs a CUDA device: there is no CPU path')
+        if isinstance(device, str):
+            device = torch.device(device).index or 0
+        self.device_index = int(device)
+        self.device = torch.device('cuda', self.device_index)
+        self.num_envs = int(num_envs)
+        self.preproc = preproc
+        self.max_episode_steps = int(max_episode_steps)
+        self.auto_reset = auto_reset
+        # one (entry point, kwargs, horizon) per env allows mixed batches (BASELINE config 5)
+        if env_ids is None:
+            self._specs = [(entry_point, dict(env_kwargs), self.max_episode_steps)] * self.num_envs
+        else:
+            self._specs = list(env_ids)
+            assert len(self._specs) == self.num_envs
+        self._horizons = np.asarray([s[2] for s in self._specs], np.int64)
+        spec = PREPROC_SPECS[preproc] if preproc is not None else dict(groups=[], kind='none', chw=False)
+        self._pspec = spec
+        groups = spec['groups']
+        self.n_channels = 3 * len(groups)
+        if obs_keys is None:
+            obs_keys = self.default_obs_keys(preproc)
+        self.obs_keys = tuple(obs_keys)
+
+        cfg = L.Config()
+        cfg.device, cfg.num_envs, cfg.n_groups, cfg.chw = self.device_index, self.num_envs, len(groups), int(spec['chw'])
+        for g, (view, age) in enumerate(groups):
+            cfg.group_view[g], cfg.group_age[g] = view, age
+        self._lib = L.lib()
+        h = C.c_void_p()
+        rc = self._lib.mg_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            raise L.MgError(f'mg_create failed ({rc}): {self._lib.mg_last_error(None).decode()}')
+        self._h = h
+        B = self.num_envs
+        with torch.cuda.device(self.device):
+            if groups:
+                shape = (B, self.n_channels, L.LORES, L.LORES) if spec['chw'] else (B, L.LORES, L.LORES, self.n_channels)
+                self._obs = torch.empty(shape, dtype=torch.uint8, device=self.device)
+            else:
+                self._obs = None
+            self._reward = torch.zeros(B, dtype=torch.float32, device=self.device)
+            self._score = torch.zeros(B, dtype=torch.float32, device=self.device)
+            self._done = torch.zeros(B, dtype=torch.uint8, device=self.device)
+            self._actions = torch.zeros(B, dtype=torch.int32, device=self.device)
+        self._extra = {}
+        self.seed(seed)
+        self._episode_steps = np.zeros(B, np.int64)
+        self.scenes = [None] * B
+        self._needs_reset = True
+
+    @staticmethod
+    def default_obs_keys(preproc):
+        if preproc is None:
+            return ('allo', 'ego')
+        if PREPROC_SPECS[preproc]['kind'] == 'stack':
+            return ('allo', 'ego')
+        return ('allo', 'ego', 'past_obs')
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return _torch().cuda.current_stream(self.device).cuda_stream
+
+    def _check(self, rc):
+        L.check(self._h, rc)
+
+    def close(self):
+        if getattr(self, '_h', None) is not None and self._h:
+            self._lib.mg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ reset
+    def seed(self, seed=None):
+        """BaseEnv.seed (base_env.py:134-141); env i gets RandomState(seed + i)."""
+        if seed is None:
+            seed = np.random.randint(0, (1 << 31) - 1)
+        self._seed = int(seed)
+        self.rngs = [np.random.RandomState((self._seed + i) % (1 << 32)) for i in range(self.num_envs)]
+        return [self._seed]
+
+    def _sample(self, i):
+        ep, kw, horizon = self._specs[i]
+        kw = dict(kw)
+        rand_dynamics = kw.pop('rand_dynamics', False)
+        for k in ('res_hw', 'fps', 'phys_steps', 'phys_iter', 'max_episode_steps'):
+            kw.pop(k, None)
+        return tasks.sample_scene(ep, self.rngs[i], horizon, rand_dynamics=rand_dynamics, **kw)
+
+    def set_scenes(self, env_ids, scenes):
+        """Install explicit initial states (used by reset and by the parity tests)."""
+        env_ids = np.ascontiguousarray(env_ids, np.int32)
+        arr = L.scenes_array(scenes)
+        self._check(self._lib.mg_set_scenes(self._h, env_ids.ctypes.data, len(scenes), C.addressof(arr), self._stream()))
+        for i, s in zip(env_ids.tolist(), scenes):
+            self.scenes[i] = L.copy_scene(s)
+            self._episode_steps[i] = 0
+
+    def reset(self, scenes=None):
+        if scenes is None:
+            scenes = [self._sample(i) for i in range(self.num_envs)]
+        self.set_scenes(np.arange(self.num_envs), scenes)
+        self._check(self._lib.mg_reset_obs(self._h, L.ptr(self._obs), self._stream()))
+        self._needs_reset = False
+        return self._make_obs()
+
+    # ------------------------------------------------------------------ step
+    def step(self, actions):
+        torch = _torch()
+        if self._needs_reset:
+            raise RuntimeError('call reset() before step()')
+        if not (isinstance(actions, torch.Tensor) and actions.is_cuda and actions.dtype == torch.int32):
+            a = np.asarray(actions).astype(np.int64).reshape(-1)
+            if a.shape[0] != self.num_envs or ((a < 0) | (a >= L.NUM_ACTIONS)).any():
+                raise KeyError(f'actions must be {self.num_envs} ints in [0, {L.NUM_ACTIONS})')
+            self._actions.copy_(torch.from_numpy(a.astype(np.int32)), non_blocking=False)
+            actions = self._actions
+        st = self._stream()
+        self._check(self._lib.mg_step_physics(self._h, L.ptr(actions), L.ptr(self._reward), L.ptr(self._done),
+                                              L.ptr(self._score), st))
+        self._episode_steps += 1
+        finished = np.nonzero(self._episode_steps >= self._horizons)[0]
+        reward, done, score = self._reward, self._done.bool(), self._score
+        if len(finished) and self.auto_reset:
+            # results of the finished episodes must survive the next step's writes
+            reward, score = reward.clone(), score.clone()
+            self.set_scenes(finished, [self._sample(int(i)) for i in finished])
+        self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
+        return self._make_obs(), reward, done, {'eval_score': score}
+
+    # ------------------------------------------------------------------ observations
+    def render_view(self, view, full_res):
+        torch = _torch()
+        n = L.RES if full_res else L.LORES
+        key = (view, bool(full_res))
+        if key not in self._extra:
+            self._extra[key] = torch.empty((self.num_envs, n, n, 3), dtype=torch.uint8, device=self.device)
+        out = self._extra[key]
+        self._check(self._lib.mg_render(self._h, int(view), int(bool(full_res)), L.ptr(out), self._stream()))
+        return out
+
+    def _make_obs(self):
+        """Observation dict in the reference's key order (allo, ego[, past_obs])."""
+        spec = self._pspec
+        obs = collections.OrderedDict()
+        if spec['kind'] == 'none':
+            for key, view in (('allo', _A), ('ego', _E)):
+                if key in self.obs_keys:
+                    obs[key] = self.render_view(view, True)
+            return obs
+        if spec['kind'] == 'stack':
+            # EagerDictFrameStack: every key becomes its own 4-frame stack (benchmarks/__init__.py:51-82)
+            if 'allo' in self.obs_keys:
+                obs['allo'] = self._obs[..., :12]
+            if 'ego' in self.obs_keys:
+                obs['ego'] = self._obs[..., 12:]
+            return obs
+        for key, view in (('allo', _A), ('ego', _E)):
+            if key in self.obs_keys:
+                img = self.render_view(view, False)
+                obs[key] = img.permute(0, 3, 1, 2) if spec['chw'] else img
+        if 'past_obs' in self.obs_keys:
+            obs['past_obs'] = self._obs
+        return obs
+
+    def render(self, mode='rgb_array'):
+        if mode != 'rgb_array':
+            raise NotImplementedError("only mode='rgb_array' is available (no window system on this box)")
+        return collections.OrderedDict(allo=self.render_view(_A, True), ego=self.render_view(_E, True))
+
+    # ------------------------------------------------------------------ state access
+    def get_bodies(self):
+        """f64 [B, 16, 6]: x, y, angle, vx, vy, w of the six robot bodies then the blocks."""
+        out = np.zeros((self.num_envs, L.MAX_BODIES, 6))
+        self._check(self._lib.mg_get_bodies(self._h, out.ctypes.data))
+        return out
+
+    def score(self):
+        torch = _torch()
+        out = torch.empty(self.num_envs, dtype=torch.float32, device=self.device)
+        self._check(self._lib.mg_score(self._h, L.ptr(out), self._stream()))
+        return out
+
+    def debug_reward(self):
+        torch = _torch()
+        out = torch.empty(self.num_envs, dtype=torch.float32, device=self.device)
+        self._check(self._lib.mg_debug_reward(self._h, L.ptr(out), self._stream()))
+        return out
+
+    def get_state(self, env_ids=None):
+        ids = np.arange(self.num_envs, dtype=np.int32) if env_ids is None else np.ascontiguousarray(env_ids, np.int32)
+        _torch().cuda.synchronize(self.device)
+        sz = self._lib.mg_state_size(self._h)
+        buf = np.zeros((len(ids), sz), np.uint8)
+        self._check(self._lib.mg_get_state(self._h, ids.ctypes.data, len(ids), buf.ctypes.data))
+        return dict(blobs=buf, episode_steps=self._episode_steps[ids].copy())
+
+    def set_state(self, state, env_ids=None):
+        ids = np.arange(self.num_envs, dtype=np.int32) if env_ids is None else np.ascontiguousarray(env_ids, np.int32)
+        buf = np.ascontiguousarray(state['blobs'], np.uint8)
+        self._check(self._lib.mg_set_state(self._h, ids.ctypes.data, len(ids), buf.ctypes.data))
+        self._episode_steps[ids] = state['episode_steps']
+        self._needs_reset = False
+
+    @property
+    def episode_steps(self):
+        return self._episode_steps.copy()
+
+    def launch_count(self):
+        return int(self._lib.mg_launch_count(self._h))
