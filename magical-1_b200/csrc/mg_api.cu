@@ -31,10 +31,10 @@ struct mg_handle {
     /* accounting */
     int64_t launches;
     int timing;
-    cudaEvent_t ev[4];
     double ms[2];
     int64_t timed_launches[2];
-    std::vector<std::pair<int, int>> pending;   /* (which, event pair index) not used: timing is synchronous */
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending[2];   /* recorded, not yet read (per kernel class) */
+    std::vector<cudaEvent_t> free_events;
     std::string err;
 };
 
@@ -111,7 +111,6 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaMalloc(&h->score_dev, (size_t)B * sizeof(float)));
     CK(h, cudaMalloc(&h->done_dev, (size_t)B));
     CK(h, cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; i++) CK(h, cudaEventCreate(&h->ev[i]));
     *out = h;
     return MG_OK;
 }
@@ -126,7 +125,8 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
     cudaStreamDestroy(h->own_stream);
-    for (int i = 0; i < 4; i++) cudaEventDestroy(h->ev[i]);
+    for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    for (auto e : h->free_events) cudaEventDestroy(e);
     delete h;
     return MG_OK;
 }
@@ -161,15 +161,25 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
     return check_launch(h, "mg_init_kernel");
 }
 
-static void time_begin(mg_handle *h, int which, cudaStream_t st) { if (h->timing) cudaEventRecord(h->ev[2 * which], st); }
+/* per-kernel timing: event pairs are recorded on the launching stream without synchronising and
+ * read back (after a synchronise) by mg_kernel_ms, so enabling it does not serialise the step */
+static void time_begin(mg_handle *h, int which, cudaStream_t st)
+{
+    if (!h->timing) return;
+    cudaEvent_t a, b;
+    if (h->free_events.size() >= 2) {
+        a = h->free_events.back(); h->free_events.pop_back();
+        b = h->free_events.back(); h->free_events.pop_back();
+    } else {
+        cudaEventCreate(&a); cudaEventCreate(&b);
+    }
+    cudaEventRecord(a, st);
+    h->pending[which].push_back(std::make_pair(a, b));
+}
 static void time_end(mg_handle *h, int which, int n_launches, cudaStream_t st)
 {
     if (!h->timing) return;
-    cudaEventRecord(h->ev[2 * which + 1], st);
-    cudaEventSynchronize(h->ev[2 * which + 1]);
-    float ms = 0;
-    cudaEventElapsedTime(&ms, h->ev[2 * which], h->ev[2 * which + 1]);
-    h->ms[which] += ms;
+    cudaEventRecord(h->pending[which].back().second, st);
     h->timed_launches[which] += n_launches;
 }
 
@@ -359,6 +369,13 @@ extern "C" int mg_set_timing(mg_handle *h, int enable) { if (!h) return MG_ERR_A
 extern "C" double mg_kernel_ms(mg_handle *h, int which, int reset, int64_t *launches_out)
 {
     if (!h || which < 0 || which > 1) return 0.0;
+    for (auto &p : h->pending[which]) {
+        float ms1 = 0;
+        cudaEventSynchronize(p.second);
+        if (cudaEventElapsedTime(&ms1, p.first, p.second) == cudaSuccess) h->ms[which] += ms1;
+        h->free_events.push_back(p.first); h->free_events.push_back(p.second);
+    }
+    h->pending[which].clear();
     double ms = h->ms[which];
     if (launches_out) *launches_out = h->timed_launches[which];
     if (reset) { h->ms[which] = 0; h->timed_launches[which] = 0; }

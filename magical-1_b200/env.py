@@ -152,6 +152,12 @@ class BatchedMagicalEnv:
             self.scenes[i] = L.copy_scene(s)
             self._episode_steps[i] = 0
 
+    def set_scenes_packed(self, env_ids, packed, n):
+        """Same as set_scenes for a pre-packed ctypes array of Scene (reset pools)."""
+        env_ids = np.ascontiguousarray(env_ids, np.int32)
+        self._check(self._lib.mg_set_scenes(self._h, env_ids.ctypes.data, int(n), C.addressof(packed), self._stream()))
+        self._episode_steps[env_ids] = 0
+
     def reset(self, scenes=None):
         if scenes is None:
             scenes = [self._sample(i) for i in range(self.num_envs)]
@@ -183,6 +189,23 @@ class BatchedMagicalEnv:
             self.set_scenes(finished, [self._sample(int(i)) for i in finished])
         self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
         return self._make_obs(), reward, done, {'eval_score': score}
+
+    def step_host(self, actions_host, obs_host, reward_host, done_host, score_host):
+        """mg_step_host: one env-step with HOST buffers (numpy / pinned torch CPU tensors); the H2D copy of
+        the actions and the D2H copies of obs / reward / done / eval_score are inside the call.
+        No auto-reset: the caller resets finished envs with set_scenes*."""
+        self._check(self._lib.mg_step_host(self._h, L.ptr(actions_host), L.ptr(obs_host), L.ptr(reward_host),
+                                           L.ptr(done_host), L.ptr(score_host)))
+        self._episode_steps += 1
+
+    def set_timing(self, enable):
+        self._check(self._lib.mg_set_timing(self._h, int(enable)))
+
+    def kernel_ms(self, which, reset=True):
+        """(accumulated CUDA-event ms, launches) of the physics (0) / render (1) kernels."""
+        n = C.c_int64(0)
+        ms = self._lib.mg_kernel_ms(self._h, int(which), int(reset), C.byref(n))
+        return float(ms), int(n.value)
 
     # ------------------------------------------------------------------ observations
     def render_view(self, view, full_res):

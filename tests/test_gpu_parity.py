@@ -10,7 +10,7 @@ from conftest import to_oracle_scene
 
 pytestmark = pytest.mark.gpu
 
-IDS = ['MoveToCorner-Demo-v0', 'MoveToCorner-TestAll-v0', 'MoveToRegion-TestAll-v0', 'MatchRegions-Demo-v0',
+IDS = ['MoveToCorner-Demo-v0', 'MoveToCorner-TestShape-v0', 'MoveToCorner-TestDynamics-v0', 'MoveToRegion-TestAll-v0', 'MatchRegions-Demo-v0',
        'MatchRegions-TestAll-v0', 'MakeLine-Demo-v0', 'MakeLine-TestAll-v0', 'FindDupe-Demo-v0',
        'FindDupe-TestLayout-v0', 'FixColour-Demo-v0', 'FixColour-TestAll-v0', 'ClusterColour-Demo-v0',
        'ClusterColour-TestAll-v0', 'ClusterShape-TestAll-v0', 'PickAndPlace-Demo-v0']
@@ -22,7 +22,7 @@ def _mixed_env(m, ids, per_id, preproc='LoRes4E', seed=0):
 
 
 def test_physics_poses_and_scores_vs_oracle(orc):
-    """100 steps of scripted random actions on 15 env ids x 4 seeds: poses 1e-3, rewards/scores 1e-5."""
+    """100 steps of scripted random actions on 16 env ids x 4 seeds: poses 1e-3, rewards/scores 1e-5."""
     import magical_b200 as m
     env, env_ids = _mixed_env(m, IDS, 4)
     env.auto_reset = False
