@@ -11,6 +11,7 @@
 #include <vector>
 #include "mg_kernels.h"
 #include "mg_tables.h"
+#include "../../include/mg_trig.h"
 
 struct mg_handle {
     mg_config cfg;
@@ -387,7 +388,7 @@ extern "C" double mg_kernel_ms(mg_handle *h, int which, int reset, int64_t *laun
 namespace {
 struct HostShape { WShape s; int ent; };   /* ent: 0 walls, 1 robot, 2+i block i, 100+i goal i */
 
-vec2 rot_of(double a) { return V(cos(a), sin(a)); }
+vec2 rot_of(double a) { double s, c; mg_sincos(a, &s, &c); return V(c, s); }
 
 int entity_shapes(const MgTables *T, const mg_scene *sc, int kind, int idx, HostShape *out)
 {

@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
+#include "../../include/mg_trig.h"
 
 struct EnvRef { double *d; int *i; };
 #define DF(e, f) ((e).d[(size_t)(f) * MG_GROUP])
@@ -45,7 +46,7 @@ __device__ void init_body(EnvRef e, int b, int dynamic, double m, double i, doub
     for (int f = 0; f < B_NF; f++) BF(e, b, f) = 0.0;
     BF(e, b, B_PX) = x; BF(e, b, B_PY) = y; BF(e, b, B_A) = a;
     double s, c;
-    sincos(a, &s, &c);
+    mg_sincos(a, &s, &c);
     BF(e, b, B_RX) = c; BF(e, b, B_RY) = s;
     BF(e, b, B_MINV) = dynamic ? 1.0 / m : 0.0;
     BF(e, b, B_IINV) = dynamic ? 1.0 / i : 0.0;
@@ -274,7 +275,7 @@ __device__ __forceinline__ vec2 vclamp_len(vec2 v, double len)
 __device__ __forceinline__ void set_angle(EnvRef e, int b, double a)
 {
     double s, c;
-    sincos(a, &s, &c);
+    mg_sincos(a, &s, &c);
     BF(e, b, B_A) = a; BF(e, b, B_RX) = c; BF(e, b, B_RY) = s;
 }
 

@@ -22,6 +22,7 @@
 #include <cuda_runtime.h>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
+#include "../../include/mg_trig.h"
 
 #define RES MG_RES
 #define BAND_ROWS 32
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             if (P.chain == MG_CHAIN_PUPIL) {
                 double rel = pose[P.body * MG_POSE_NF + 2] - rp[2];   /* pupil.angle - robot.angle, entities.py:489-491 */
                 double sn, cs;
-                sincos(rel, &sn, &cs);
+                mg_sincos(rel, &sn, &cs);
                 M = aff_mul(M, aff_tr(0.0, 0.0, cs, sn));
                 M = aff_mul(M, aff_tr(0.0, radius * 0.07, 1.0, 0.0));
             }

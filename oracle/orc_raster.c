@@ -14,6 +14,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "orc.h"
+#include "../include/mg_trig.h"
 
 #define RES MG_RES
 
@@ -37,7 +38,8 @@ static aff aff_mul(aff A, aff B)
 static aff transform_make(double tx, double ty, double rot, double sx, double sy)
 {
     aff T = { 1.0, 0.0, tx, 0.0, 1.0, ty };
-    double cs = cos(rot), sn = sin(rot);
+    double cs, sn;   /* np.cos / np.sin in the reference; shared mg_sincos here (see orc_scene.c) */
+    mg_sincos(rot, &sn, &cs);
     aff R = { cs, -sn, 0.0, sn, cs, 0.0 };
     aff S = { sx, 0.0, 0.0, 0.0, sy, 0.0 };
     return aff_mul(aff_mul(T, R), S);

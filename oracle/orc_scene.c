@@ -12,15 +12,17 @@
 #include <stdlib.h>
 #include <string.h>
 #include "orc.h"
+#include "../include/mg_trig.h"
 
 #define CP_ALL_CATEGORIES 0xffffffffu
 
 void orc_body_set_angle(orc_body *b, double a)
 {
-    /* cpBodySetAngle -> SetAngle + SetTransform: rot = cpvforangle(a) */
+    /* cpBodySetAngle -> SetAngle + SetTransform: rot = cpvforangle(a).  Chipmunk calls libm here; the
+     * oracle and the CUDA kernels share include/mg_trig.h (<= 1 ulp from glibc) so that both sides of a
+     * parity test see bit-identical rotations. */
     b->a = a;
-    b->rot.x = cos(a);
-    b->rot.y = sin(a);
+    mg_sincos(a, &b->rot.y, &b->rot.x);
 }
 
 static int add_body(orc_env *e, int type, double m, double i, double x, double y, double a)

@@ -47,6 +47,7 @@ def test_physics_poses_and_scores_vs_oracle(orc):
             exp_rew = o.debug_reward() if o.scene.debug_reward else exp_score
             assert abs(score[i] - exp_score) <= 1e-5, (env_ids[i], t, score[i], exp_score)
             assert abs(rew[i] - exp_rew) <= 1e-5, (env_ids[i], t, rew[i], exp_rew)
+    print('max pose error over 100 steps:', max_err.max())
     bad = [(env_ids[i], float(max_err[i])) for i in range(B) if max_err[i] > 1e-3]
     assert not bad, bad
     env.close()
