@@ -208,6 +208,7 @@ MG_HD vec2 seg_closest(vec2 a, vec2 b, vec2 p, double *t_out)
  * from A to B, d is the signed core separation. */
 MG_HDN inline void convex_axis(const WShape *A, const WShape *B, vec2 *n_out, double *d_out)
 {
+    const double rsum = A->r + B->r;
     double best = -INFINITY;
     vec2 axis = V(1.0, 0.0);
     for (int i = 0; i < A->n; i++) {
@@ -229,6 +230,9 @@ MG_HDN inline void convex_axis(const WShape *A, const WShape *B, vec2 *n_out, do
         if (sep > best) { best = sep; axis = vneg(fn); }
     }
     if (best <= 0.0) { *n_out = axis; *d_out = best; return; }
+    /* A face separation is a lower bound of the true distance: beyond r_a + r_b the pair cannot touch and
+     * the caller discards (n, d), so the closest-feature search is skipped (same contacts as without it). */
+    if (best > rsum) { *n_out = axis; *d_out = best; return; }
 
     double bestd2 = INFINITY;
     vec2 bn = axis;
@@ -346,6 +350,8 @@ MG_HDN inline void collide_circle_poly(const WShape *c, const WShape *p, Manifol
     vec2 nrm, pb; double d;
     if (best <= 0.0) {
         nrm = vneg(p->nrm[bi]); d = best; pb = vsub(center, vmul(p->nrm[bi], best));
+    } else if (best > c->r + p->r) {
+        return;     /* face separation already exceeds r_c + r_p: no contact (see convex_axis) */
     } else {
         double bestd2 = INFINITY;
         nrm = vneg(p->nrm[bi]); d = best; pb = center;

@@ -93,6 +93,7 @@ struct WarpSmem {
     int vx[MG_CIRCLE_RES + 4], vy[MG_CIRCLE_RES + 4];
     double fx[4], fy[4];                     /* float vertices (dashed outlines only) */
     uint8_t lo[LO_BAND_BYTES];               /* downsampled band, HWC */
+    int span_lo[BAND_ROWS], span_hi[BAND_ROWS], span_cnt[BAND_ROWS];   /* per-row crossings (edge-parallel fill) */
 };
 
 /* ---------------------------------------------------------------- lines (pygame draw.c) */
@@ -131,7 +132,22 @@ __device__ bool clipline(int &x1, int &y1, int &x2, int &y2)
 /* One clipped line = pixels k = 0..len-1 of pygame's integer DDA (drawline / drawhorzline /
  * drawvertline produce the same set): the major axis advances by one per pixel, the minor
  * axis by floor(k * minor_len / major_len). */
-struct Line { int x1, y1, sx, sy, dxp, dyp, len; bool xmajor; };
+struct Line { int x1, y1, sx, sy, dxp, dyp, len; bool xmajor; float rmaj; };
+
+/* floor(a / b) for 0 <= a < 2^24, 0 < b: one float multiply and a +-1 correction instead of an integer divide */
+__device__ __forceinline__ int div_small(int a, int b, float rb)
+{
+    int q = (int)((float)a * rb);
+    int r = a - q * b;
+    if (r < 0) q--; else if (r >= b) q++;
+    return q;
+}
+/* C integer division (truncation toward zero) of num by den > 0 */
+__device__ __forceinline__ int div_trunc(int num, int den)
+{
+    float rb = __frcp_rn((float)den);
+    return num >= 0 ? div_small(num, den, rb) : -div_small(-num, den, rb);
+}
 
 __device__ __forceinline__ bool line_setup(int x1, int y1, int x2, int y2, Line &L)
 {
@@ -143,12 +159,13 @@ __device__ __forceinline__ bool line_setup(int x1, int y1, int x2, int y2, Line 
     L.x1 = x1; L.y1 = y1;
     L.xmajor = !(L.dxp < L.dyp);
     L.len = L.xmajor ? L.dxp : L.dyp;
+    L.rmaj = __frcp_rn((float)L.len);
     return true;
 }
 __device__ __forceinline__ void line_pixel(const Line &L, int k, int &x, int &y)
 {
-    if (L.xmajor) { x = L.x1 + L.sx * k; y = L.y1 + L.sy * ((k * L.dyp) / L.dxp); }
-    else { y = L.y1 + L.sy * k; x = L.x1 + L.sx * ((k * L.dxp) / L.dyp); }
+    if (L.xmajor) { x = L.x1 + L.sx * k; y = L.dyp == 1 ? L.y1 : L.y1 + L.sy * div_small(k * L.dyp, L.dxp, L.rmaj); }
+    else { y = L.y1 + L.sy * k; x = L.dxp == 1 ? L.x1 : L.x1 + L.sx * div_small(k * L.dxp, L.dyp, L.rmaj); }
 }
 __device__ __forceinline__ void put_px(uint8_t *buf, int y0, int x, int y, uint8_t c)
 {
@@ -234,6 +251,18 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
     }
 }
 
+/* drawhorzlineclip: inclusive span [lo, hi] of one row, clipped to the surface; word stores inside */
+__device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t c)
+{
+    if (hi < 0 || lo > RES - 1) return;
+    lo = max(lo, 0); hi = min(hi, RES - 1);
+    uint32_t c4 = c * 0x01010101u;
+    int x = lo;
+    while (x <= hi && (x & 3)) row[x++] = c;
+    for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
+    for (; x <= hi; x++) row[x] = c;
+}
+
 /* pygame.draw.polygon fill of rows [y0, y0+32): lane r owns row y0 + r */
 __device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
 {
@@ -252,36 +281,66 @@ __device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, i
             else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
             else continue;
             if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
-                int x = (y - y1) * (x2 - x1) / (y2 - y1) + x1;
+                int x = div_trunc((y - y1) * (x2 - x1), y2 - y1) + x1;
                 lo = min(lo, x); hi = max(hi, x); cnt++;
             }
         }
     }
     if (cnt < 2) return;
-    if (hi < 0 || lo > RES - 1) return;
-    lo = max(lo, 0); hi = min(hi, RES - 1);
-    uint8_t *row = W->buf + lane * ROW_STRIDE;
-    uint32_t c4 = c * 0x01010101u;
-    int x = lo;
-    while (x <= hi && (x & 3)) row[x++] = c;
-    for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
-    for (; x <= hi; x++) row[x] = c;
+    fill_span(W->buf + lane * ROW_STRIDE, lo, hi, c);
+}
+
+/* same fill for polygons with many edges (the 100-gon circles): lanes take edges, every edge adds its
+ * crossings to the rows of the band it spans; then lane r fills row r.  Same spans as the row-parallel form. */
+__device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
+{
+    W->span_lo[lane] = 0x7fffffff; W->span_hi[lane] = -0x7fffffff - 1; W->span_cnt[lane] = 0;
+    __syncwarp();
+    if (miny == maxy) {
+        int lo = 0x7fffffff, hi = -0x7fffffff - 1;
+        for (int i = lane; i < n; i += 32) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
+        lo = __reduce_min_sync(FULL, lo); hi = __reduce_max_sync(FULL, hi);
+        unsigned r = (unsigned)(miny - y0);
+        if (r == (unsigned)lane) { W->span_lo[lane] = lo; W->span_hi[lane] = hi; W->span_cnt[lane] = 2; }
+    } else {
+        for (int i = lane; i < n; i += 32) {
+            int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
+            int x1, y1, x2, y2;
+            if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
+            else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
+            else continue;
+            /* rows with (y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2) */
+            int ylast = y2 == maxy ? y2 : y2 - 1;
+            int ya_ = max(y1, y0), yb_ = min(ylast, y0 + BAND_ROWS - 1);
+            float rb = __frcp_rn((float)(y2 - y1));
+            for (int y = ya_; y <= yb_; y++) {
+                int num = (y - y1) * (x2 - x1);
+                int x = (num >= 0 ? div_small(num, y2 - y1, rb) : -div_small(-num, y2 - y1, rb)) + x1;
+                atomicMin(&W->span_lo[y - y0], x);
+                atomicMax(&W->span_hi[y - y0], x);
+                atomicAdd(&W->span_cnt[y - y0], 1);
+            }
+        }
+    }
+    __syncwarp();
+    if (W->span_cnt[lane] >= 2) fill_span(W->buf + lane * ROW_STRIDE, W->span_lo[lane], W->span_hi[lane], c);
 }
 
 __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3)
 {
-    /* 16 palette ids -> per-channel sums -> round-half-even(sum / 16), packed r | g<<8 | b<<16 */
-    uint32_t rs = 0, gs = 0, bs = 0;
+    /* 16 palette ids -> per-channel sums (r and b share one register) -> round-half-even(sum / 16),
+     * packed r | g<<8 | b<<16 */
+    uint32_t rb = 0, gs = 0;
     uint32_t ws[4] = { w0, w1, w2, w3 };
 #pragma unroll
     for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             uint32_t p = pal[(ws[i] >> (8 * j)) & 31];
-            rs += p & 255; gs += (p >> 8) & 255; bs += (p >> 16) & 255;
+            rb += p & 0x00ff00ffu; gs += (p >> 8) & 255u;
         }
     uint32_t out = 0;
-    uint32_t s[3] = { rs, gs, bs };
+    uint32_t s[3] = { rb & 0xffffu, gs, rb >> 16 };
 #pragma unroll
     for (int k = 0; k < 3; k++) {
         uint32_t q = s[k] >> 4, r = s[k] & 15;
@@ -289,6 +348,17 @@ __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, 
         out |= q << (8 * k);
     }
     return out;
+}
+
+/* bytes 3p .. 3p+2 of the 12-byte group (s0, s1, s2): the RGB of pixel p of four consecutive pixels */
+__device__ __forceinline__ uint32_t rgb_of(uint32_t s0, uint32_t s1, uint32_t s2, int p)
+{
+    switch (p) {
+    case 0: return s0 & 0xffffffu;
+    case 1: return __funnelshift_r(s0, s1, 24) & 0xffffffu;
+    case 2: return __funnelshift_r(s1, s2, 16) & 0xffffffu;
+    default: return s2 >> 8;
+    }
 }
 
 struct RenderArgs {
@@ -386,7 +456,8 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         __syncwarp();
         /* outlines reach at most 2 pixels beyond the vertex rows */
         if (maxy + 2 >= y0 && miny - 2 < y0 + BAND_ROWS) {
-            fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
+            if (n <= 8) fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
+            else fill_poly_band_edges(W, y0, lane, n, miny, maxy, P.fill);
             __syncwarp();
             if (P.mode == 1) {
                 /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
@@ -467,6 +538,36 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
      * by this very launch (age 0, or any age of a fresh env) come from shared memory. */
     const int G = A.n_groups, C = 3 * G;
     uint32_t *obs_w = (uint32_t *)(A.obs + ((size_t)env * MG_LORES * MG_LORES + (size_t)band * LO_ROWS * MG_LORES) * C);
+    if (G == 4) {
+        /* LoRes4E / LoRes4A: 4 frames x RGB = 12 bytes per pixel; a lane turns 4 pixels of each frame
+         * (3 words each) into 48 contiguous output bytes = three 16-byte stores */
+        const uint32_t *srcp[4];
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+            if (A.gview[g] == A.view && (A.gage[g] == 0 || fresh)) srcp[g] = (const uint32_t *)W->lo;
+            else srcp[g] = (const uint32_t *)(S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES + band_off);
+        }
+#pragma unroll 3
+        for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {
+            uint32_t src[4][3];
+#pragma unroll
+            for (int g = 0; g < 4; g++) { src[g][0] = srcp[g][q * 3]; src[g][1] = srcp[g][q * 3 + 1]; src[g][2] = srcp[g][q * 3 + 2]; }
+            uint4 *dst = (uint4 *)(obs_w + (size_t)q * 12);
+#pragma unroll
+            for (int half = 0; half < 3; half++) {
+                uint32_t o[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    int w = half * 4 + k, px = w / 3, part = w % 3;   /* word w of the 12 output words */
+                    uint32_t t0 = rgb_of(src[part][0], src[part][1], src[part][2], px);
+                    uint32_t t1 = rgb_of(src[part + 1][0], src[part + 1][1], src[part + 1][2], px);
+                    o[k] = part == 0 ? (t0 | (t1 << 24)) : (part == 1 ? ((t0 >> 8) | (t1 << 16)) : ((t0 >> 16) | (t1 << 8)));
+                }
+                dst[half] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+        }
+        return;
+    }
     for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {      /* q = group of 4 consecutive pixels */
         uint32_t src[MG_MAX_GROUPS][3];
         for (int g = 0; g < G; g++) {

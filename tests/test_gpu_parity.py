@@ -64,12 +64,14 @@ def test_full_res_render_vs_oracle(orc, view):
     actions = np.random.RandomState(7).randint(0, 18, size=(7, env.num_envs))
     for phase in range(2):
         img = env.render_view(view, True).cpu().numpy()
-        worst = 0.0
+        worst, n_any = 0.0, 0
         for i, o in enumerate(oracles):
             want = o.render(view)
             frac = (np.abs(img[i].astype(int) - want.astype(int)).max(axis=-1) > 8).mean()
+            n_any += int((img[i] != want).any(axis=-1).sum())
             worst = max(worst, frac)
             assert frac <= 0.01, (env_ids[i], phase, frac)
+        print(f'view {view} phase {phase}: worst >8-level fraction {worst:.6f}, pixels differing at all {n_any}')
         if phase == 0:
             for t in range(7):
                 env.step(actions[t])
