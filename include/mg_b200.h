@@ -24,6 +24,7 @@
  *   mg_get_state/mg_set_state (no reference equivalent: EzPickle re-constructs, base_env.py:20-46)
  *   mg_host_entity_overlaps   space.shape_query in the placement     magical/geom.py:226-233
  *                             sampler (host-side reset only)
+ *   mg_host_palette           style.COLOURS_RGB / darken / lighten   magical/style.py:10-37
  *
  * Conventions: plain pointers and sizes; no exceptions cross the boundary; every call
  * returns 0 on success or a negative MG_ERR_* code and records a message readable with
@@ -134,6 +135,12 @@ enum { MG_ENT_ROBOT = 0, MG_ENT_BLOCK = 1, MG_ENT_GOAL = 2 };
  * geom.pm_randomise_pose (geom.py:226-233); touching counts (distance <= 0). */
 int mg_host_entity_overlaps(const mg_scene *scene, int kind, int idx, int robot_active,
                             uint32_t block_mask, uint32_t goal_mask);
+
+/* The 18 palette entries the renderer draws with, u8 RGB each, in the order
+ * background, white, grey, dark grey, light grey (finger inner), pupil, then colour / darkened colour /
+ * twice-lightened colour for red, green, blue, yellow (magical/style.py:10-37, render.py:146-149).
+ * Returns the number of entries written to rgb_out[n][3]. */
+int mg_host_palette(uint8_t *rgb_out);
 
 #ifdef __cplusplus
 }

@@ -79,6 +79,7 @@ SYMBOLS = {
     'mg_launch_count': (C.c_int64, [_VP]),
     'mg_set_timing': (C.c_int, [_VP, C.c_int]),
     'mg_kernel_ms': (C.c_double, [_VP, C.c_int, C.c_int, C.POINTER(C.c_int64)]),
+    'mg_host_palette': (C.c_int, [_VP]),
     'mg_host_entity_overlaps': (C.c_int, [C.POINTER(Scene), C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32]),
 }
 

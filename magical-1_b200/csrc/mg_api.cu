@@ -468,3 +468,11 @@ extern "C" int mg_host_entity_overlaps(const mg_scene *scene, int kind, int idx,
     }
     return 0;
 }
+
+extern "C" int mg_host_palette(uint8_t *rgb_out)
+{
+    const MgTables *T = mg_tables_host();
+    for (int i = 0; i < MG_PAL_COUNT; i++)
+        for (int k = 0; k < 3; k++) rgb_out[i * 3 + k] = T->pal[i][k];
+    return MG_PAL_COUNT;
+}
