@@ -98,6 +98,9 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     for (int v = 0; v < 2; v++) {
         CK(h, cudaMalloc(&h->S.ring[v], (size_t)B * MG_MAX_RING * MG_FRAME_BYTES));
         CK(h, cudaMemset(h->S.ring[v], 0, (size_t)B * MG_MAX_RING * MG_FRAME_BYTES));
+        CK(h, cudaMalloc(&h->S.sprims[v], (size_t)B * MG_MAX_PRIMS * sizeof(MgScreenPrim)));
+        CK(h, cudaMalloc(&h->S.sverts[v], (size_t)B * MG_MAX_VERTS * sizeof(int2)));
+        CK(h, cudaMalloc(&h->S.dashv[v], (size_t)B * MG_MAX_GOALS * 8 * sizeof(double)));
     }
     CK(h, cudaMalloc(&h->tables_dev, sizeof(MgTables)));
     CK(h, cudaMemcpy(h->tables_dev, mg_tables_host(), sizeof(MgTables), cudaMemcpyHostToDevice));
@@ -123,6 +126,7 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaDeviceSynchronize();
     cudaFree(h->S.dstate); cudaFree(h->S.istate); cudaFree(h->S.scenes); cudaFree(h->S.prims);
     cudaFree(h->S.n_prims); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
+    for (int v = 0; v < 2; v++) { cudaFree(h->S.sprims[v]); cudaFree(h->S.sverts[v]); cudaFree(h->S.dashv[v]); }
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
     cudaStreamDestroy(h->own_stream);
@@ -213,7 +217,8 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
         mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, st);
         nl++;
     }
-    time_end(h, 1, nl, st);
+    time_end(h, 1, nl, st);      /* one timed unit = geometry + raster launch of one view */
+    nl *= 2;
     if (!h->fused && obs_dev && h->spec.n_groups > 0) { mg_launch_compose(h->S, h->spec, h->slots, obs_dev, st); nl++; }
     mg_launch_clear_fresh(h->S, st); nl++;
     h->launches += nl;
@@ -253,7 +258,7 @@ extern "C" int mg_render(mg_handle *h, int view, int full_res, uint8_t *out_dev,
     if (!h || !out_dev || view < 0 || view > 1) return fail(h, MG_ERR_ARG, "mg_render: bad argument");
     CK(h, cudaSetDevice(h->cfg.device));
     mg_launch_render_out(h->S, view, full_res, out_dev, (cudaStream_t)stream);
-    h->launches++;
+    h->launches += 2;            /* geometry + raster */
     return check_launch(h, "mg_render_kernel");
 }
 

@@ -105,6 +105,7 @@ struct MgTables {
     double spring_w_coef;        /* 1 - exp(-damping * dt * (robot.i_inv + pupil.i_inv)) */
     /* draw lists */
     int dl_off[MG_DL_COUNT], dl_n[MG_DL_COUNT];
+    double dl_rad[MG_DL_COUNT];  /* max |vertex| of the list: pre-transform band cull in the rasteriser */
     vec2 dl_pool[4 * MG_CIRCLE_RES + 160];
     uint8_t pal[32][4];
 };

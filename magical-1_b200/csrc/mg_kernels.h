@@ -22,6 +22,10 @@ struct MgDeviceState {
     /* frame stacks: ring[view] = u8 [B][MG_MAX_RING][96][96][3]; the newest slot is the same for all envs
      * (every env pushes one frame per step) and is tracked on the host */
     uint8_t *ring[2];
+    /* screen-space geometry of the current poses, per view (mg_geometry_kernel -> mg_render_kernel) */
+    MgScreenPrim *sprims[2]; /* [B][MG_MAX_PRIMS] */
+    int2 *sverts[2];         /* [B][MG_MAX_VERTS] truncated vertices */
+    double *dashv[2];        /* [B][MG_MAX_GOALS][4][2] untruncated goal-region vertices (dashed outlines) */
 };
 
 struct MgObsSpec {
@@ -39,6 +43,9 @@ void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaS
  * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v) */
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
                            uint8_t *obs, cudaStream_t st);
+/* transform every primitive of every env into the screen space of `view` (must precede the render launches
+ * of that view whenever poses or scenes changed) */
+void mg_launch_geometry(const MgDeviceState &S, int view, cudaStream_t st);
 /* compose the stacked observation from the rings (any view mix, HWC or CHW) */
 void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int *slots, uint8_t *obs, cudaStream_t st);
 /* clear the per-env "fresh" flag after all views were pushed */

@@ -16,6 +16,7 @@
  * (mg_state.cuh), so every state access of a warp is one 256-byte row.
  */
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
@@ -939,9 +940,12 @@ __device__ double env_debug_reward(EnvRef e)
 
 /* BaseEnv.step up to (not including) render */
 __global__ void __launch_bounds__(32) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
-                                                        uint8_t *done_out, float *score_out)
+                                                        uint8_t *done_out, float *score_out, int envs_per_warp)
 {
-    int env = blockIdx.x * blockDim.x + threadIdx.x;
+    /* one thread per env, but only envs_per_warp lanes of each warp carry one: an env-step is a long serial,
+     * branchy chain, so fewer envs per warp = less divergence and more warps to hide its latency with */
+    if ((int)threadIdx.x >= envs_per_warp) return;
+    int env = blockIdx.x * envs_per_warp + threadIdx.x;
     if (env >= S.num_envs) return;
     const MgTables *T = S.tables;
     EnvRef e = env_ref(S.dstate, S.istate, env);
@@ -1022,7 +1026,9 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
 }
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st)
 {
-    mg_physics_kernel<<<(S.num_envs + 31) / 32, 32, 0, st>>>(S, actions, reward, done, score);
+    static int epw = 0;
+    if (!epw) { const char *v = getenv("MG_PHYS_EPW"); epw = v ? atoi(v) : 8; if (epw < 1 || epw > 32) epw = 8; }
+    mg_physics_kernel<<<(S.num_envs + epw - 1) / epw, 32, 0, st>>>(S, actions, reward, done, score, epw);
 }
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
 {

@@ -25,9 +25,12 @@
 #include "../../include/mg_trig.h"
 
 #define RES MG_RES
+#ifndef BAND_ROWS
 #define BAND_ROWS 32
+#endif
 #define N_BANDS (RES / BAND_ROWS)
 #define ROW_STRIDE 388                       /* 97 words: lane-per-row word stores are bank-conflict free */
+#define ROW_PARTS (32 / BAND_ROWS)            /* lanes that share one row in the polygon fills */
 #define LO_ROWS (BAND_ROWS / 4)
 #define LO_BAND_BYTES (LO_ROWS * MG_LORES * 3)   /* 2304 */
 #define WARPS_PER_CTA 4
@@ -251,11 +254,20 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
     }
 }
 
-/* drawhorzlineclip: inclusive span [lo, hi] of one row, clipped to the surface; word stores inside */
-__device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t c)
+/* drawhorzlineclip: inclusive span [lo, hi] of one row, clipped to the surface; word stores inside.
+ * The 32 / BAND_ROWS lanes that share a row (part = 0 .. ROW_PARTS-1) split the span at word boundaries. */
+__device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t c, int part)
 {
     if (hi < 0 || lo > RES - 1) return;
     lo = max(lo, 0); hi = min(hi, RES - 1);
+    if (ROW_PARTS > 1) {
+        int chunk = (((hi - lo + 1) + ROW_PARTS - 1) / ROW_PARTS + 3) & ~3;
+        int a = lo + part * chunk;
+        if (part > 0) a &= ~3;
+        int b = (lo + (part + 1) * chunk) & ~3;
+        lo = a; hi = part == ROW_PARTS - 1 ? hi : min(hi, b - 1);
+        if (lo > hi) return;
+    }
     uint32_t c4 = c * 0x01010101u;
     int x = lo;
     while (x <= hi && (x & 3)) row[x++] = c;
@@ -263,10 +275,11 @@ __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t 
     for (; x <= hi; x++) row[x] = c;
 }
 
-/* pygame.draw.polygon fill of rows [y0, y0+32): lane r owns row y0 + r */
+/* pygame.draw.polygon fill of rows [y0, y0 + BAND_ROWS): lane owns row y0 + lane % BAND_ROWS */
 __device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
 {
-    int y = y0 + lane;
+    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
+    int y = y0 + row;
     if (y < miny || y > maxy) return;
     int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
     if (miny == maxy) {
@@ -287,21 +300,22 @@ __device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, i
         }
     }
     if (cnt < 2) return;
-    fill_span(W->buf + lane * ROW_STRIDE, lo, hi, c);
+    fill_span(W->buf + row * ROW_STRIDE, lo, hi, c, part);
 }
 
 /* same fill for polygons with many edges (the 100-gon circles): lanes take edges, every edge adds its
- * crossings to the rows of the band it spans; then lane r fills row r.  Same spans as the row-parallel form. */
+ * crossings to the rows of the band it spans; then the row's lanes fill it.  Same spans as the row-parallel form. */
 __device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
 {
-    W->span_lo[lane] = 0x7fffffff; W->span_hi[lane] = -0x7fffffff - 1; W->span_cnt[lane] = 0;
+    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
+    if (lane < BAND_ROWS) { W->span_lo[lane] = 0x7fffffff; W->span_hi[lane] = -0x7fffffff - 1; W->span_cnt[lane] = 0; }
     __syncwarp();
     if (miny == maxy) {
         int lo = 0x7fffffff, hi = -0x7fffffff - 1;
         for (int i = lane; i < n; i += 32) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
         lo = __reduce_min_sync(FULL, lo); hi = __reduce_max_sync(FULL, hi);
         unsigned r = (unsigned)(miny - y0);
-        if (r == (unsigned)lane) { W->span_lo[lane] = lo; W->span_hi[lane] = hi; W->span_cnt[lane] = 2; }
+        if (r == (unsigned)lane && lane < BAND_ROWS) { W->span_lo[lane] = lo; W->span_hi[lane] = hi; W->span_cnt[lane] = 2; }
     } else {
         for (int i = lane; i < n; i += 32) {
             int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
@@ -323,7 +337,7 @@ __device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int m
         }
     }
     __syncwarp();
-    if (W->span_cnt[lane] >= 2) fill_span(W->buf + lane * ROW_STRIDE, W->span_lo[lane], W->span_hi[lane], c);
+    if (W->span_cnt[row] >= 2) fill_span(W->buf + row * ROW_STRIDE, W->span_lo[row], W->span_hi[row], c, part);
 }
 
 __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3)
@@ -372,35 +386,29 @@ struct RenderArgs {
     int gview[MG_MAX_GROUPS], gslot[MG_MAX_GROUPS], gage[MG_MAX_GROUPS];
 };
 
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceState S, RenderArgs A)
+/* ---------------------------------------------------------------- geometry pass
+ * One warp per env: walks the env's draw list once per view, builds each primitive's transform chain
+ * (Viewer.render -> Geom.render -> stack.apply_current_matrix, render.py:116-160, 373-392), transforms the
+ * vertices in FP64 and truncates them the way pygame converts its float arguments to int.  The band
+ * rasterisers then only see integers. */
+__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __shared__ uint32_t pal[32];
     const MgTables *T = S.tables;
-    if (threadIdx.x < 32) {
-        const uint8_t *p = T->pal[threadIdx.x];
-        pal[threadIdx.x] = p[0] | (p[1] << 8) | (p[2] << 16);
-    }
-    __syncthreads();
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
-    int env = (int)(item / N_BANDS), band = (int)(item % N_BANDS);
+    const int lane = threadIdx.x & 31;
+    const int env = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (env >= S.num_envs) return;
-    WarpSmem *W = (WarpSmem *)smem_raw + warp;
-    const int y0 = band * BAND_ROWS;
     const double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
     const double *rp = pose + MG_BODY_ROBOT * MG_POSE_NF;
-
-    /* Viewer._clear: background */
-    for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 4; i += 32) ((uint32_t *)W->buf)[i] = MG_PAL_BG * 0x01010101u;
-    aff cam = A.view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
-    aff cam_robot = aff_mul(cam, aff_tr(rp[0], rp[1], rp[6], rp[7]));
-    __syncwarp();
-
+    const aff cam = view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
+    const aff cam_robot = aff_mul(cam, aff_tr(rp[0], rp[1], rp[6], rp[7]));
     const MgPrim *prims = S.prims + (size_t)env * MG_MAX_PRIMS;
-    int np = S.n_prims[env];
+    MgScreenPrim *sprims = S.sprims[view] + (size_t)env * MG_MAX_PRIMS;
+    int2 *sverts = S.sverts[view] + (size_t)env * MG_MAX_VERTS;
+    double *dashv = S.dashv[view] + (size_t)env * MG_MAX_GOALS * 8;
+    const int np = S.n_prims[env];
+    int off = 0;
     for (int pi = 0; pi < np; pi++) {
-        MgPrim P = prims[pi];
+        const MgPrim P = prims[pi];
         aff M;
         const vec2 *lv = T->dl_pool + T->dl_off[P.dl];
         int n = T->dl_n[P.dl];
@@ -433,8 +441,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             break;
         }
         }
+        if (off + n > MG_MAX_VERTS) n = 0;      /* cannot happen for scenes mg_set_scenes accepts */
         /* transform + truncate vertices (stack.apply_current_matrix, then pygame's int conversion) */
-        int miny = 0x7fffffff, maxy = -0x7fffffff - 1;
+        int miny = 0x7fffffff, maxy = -0x7fffffff - 1, minx = 0x7fffffff, maxx = -0x7fffffff - 1;
         for (int i = lane; i < n; i += 32) {
             double x, y;
             if (P.chain == MG_CHAIN_GOAL) {
@@ -445,17 +454,91 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             double fx = (M.a * x + M.b * y) + M.tx;
             double fy = (M.c * x + M.d * y) + M.ty;
             int ix = (int)fx, iy = (int)fy;
-            W->vx[i] = ix; W->vy[i] = iy;
-            if (n <= 4) { W->fx[i] = fx; W->fy[i] = fy; }
+            sverts[off + i] = make_int2(ix, iy);
+            if (P.mode == 2 && i < 4) { dashv[P.aux * 8 + 2 * i] = fx; dashv[P.aux * 8 + 2 * i + 1] = fy; }
             miny = min(miny, iy); maxy = max(maxy, iy);
+            minx = min(minx, ix); maxx = max(maxx, ix);
         }
-        miny = __reduce_min_sync(FULL, miny);
-        maxy = __reduce_max_sync(FULL, maxy);
-        __syncwarp();
-        if (lane == 0) { W->vx[n] = W->vx[0]; W->vy[n] = W->vy[0]; }
-        __syncwarp();
+        miny = __reduce_min_sync(FULL, miny); maxy = __reduce_max_sync(FULL, maxy);
+        minx = __reduce_min_sync(FULL, minx); maxx = __reduce_max_sync(FULL, maxx);
+        /* nothing of a primitive whose vertices all lie more than 4 pixels outside the surface can reach it
+         * (fills are clipped per row, outline copies are shifted by at most 2 and clipped) */
+        bool visible = n > 0 && maxy >= -4 && miny <= RES + 3 && maxx >= -4 && minx <= RES + 3;
+        if (lane == 0) {
+            MgScreenPrim sp;
+            sp.off_n = visible ? (off << 8 | n) : 0;
+            sp.miny = miny; sp.maxy = maxy;
+            sp.style = (uint32_t)P.fill | (uint32_t)P.outline << 8 | (uint32_t)P.mode << 16 | (uint32_t)P.aux << 24;
+            sprims[pi] = sp;
+        }
+        if (visible) off += n;
+    }
+}
+
+/* VARIANT selects what happens to the finished band, so that each instantiation carries only its own tail
+ * (the kernel is instruction-cache sensitive): 0 push into the ring; 1 push + fused 4-group HWC stack;
+ * 2 push + fused generic HWC stack; 3 lo-res frame out; 4 full-res frame out */
+template <int VARIANT>
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceState S, RenderArgs A)
+{
+    constexpr int MODE = VARIANT <= 2 ? 0 : VARIANT - 2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t pal[32];
+    const MgTables *T = S.tables;
+    if (threadIdx.x < 32) {
+        const uint8_t *p = T->pal[threadIdx.x];
+        pal[threadIdx.x] = p[0] | (p[1] << 8) | (p[2] << 16);
+    }
+    __syncthreads();
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
+    int env = (int)(item / N_BANDS), band = (int)(item % N_BANDS);
+    if (env >= S.num_envs) return;
+    WarpSmem *W = (WarpSmem *)smem_raw + warp;
+    const int y0 = band * BAND_ROWS;
+
+    /* the fused stack reads three older frames of this band from the ring at the very end: start pulling
+     * their lines towards L2 now (18 lines of 128 B per frame band) */
+    if (VARIANT >= 1 && VARIANT <= 2 && lane < LO_BAND_BYTES / 128) {
+#pragma unroll
+        for (int g = 0; g < MG_MAX_GROUPS; g++) {
+            if (g >= A.n_groups || (A.gview[g] == A.view && A.gage[g] == 0)) continue;
+            const uint8_t *p = S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES
+                               + (size_t)band * LO_BAND_BYTES + lane * 128;
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+        }
+    }
+    /* Viewer._clear: background */
+    for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 4; i += 32) ((uint32_t *)W->buf)[i] = MG_PAL_BG * 0x01010101u;
+    __syncwarp();
+
+    /* primitives in draw order, 32 headers per coalesced load; each lane tests its own primitive against
+     * the band and the warp then walks the hits in order (painter's algorithm) */
+    const MgScreenPrim *sprims = S.sprims[A.view] + (size_t)env * MG_MAX_PRIMS;
+    const int2 *sverts = S.sverts[A.view] + (size_t)env * MG_MAX_VERTS;
+    const int np = S.n_prims[env];
+    for (int base = 0; base < np; base += 32) {
+        MgScreenPrim mine = { 0, 0x7fffffff, -0x7fffffff - 1, 0 };
+        if (base + lane < np) mine = sprims[base + lane];
         /* outlines reach at most 2 pixels beyond the vertex rows */
-        if (maxy + 2 >= y0 && miny - 2 < y0 + BAND_ROWS) {
+        unsigned hits = __ballot_sync(FULL, (mine.off_n & 255) != 0 && mine.maxy + 2 >= y0 && mine.miny - 2 < y0 + BAND_ROWS);
+      while (hits) {
+        const int src = __ffs(hits) - 1;
+        hits &= hits - 1;
+        const int off_n = __shfl_sync(FULL, mine.off_n, src);
+        const int miny = __shfl_sync(FULL, mine.miny, src), maxy = __shfl_sync(FULL, mine.maxy, src);
+        const uint32_t style = __shfl_sync(FULL, mine.style, src);
+        const int n = off_n & 255;
+        struct { uint8_t fill, outline, mode, aux; } P = { (uint8_t)style, (uint8_t)(style >> 8), (uint8_t)(style >> 16), (uint8_t)(style >> 24) };
+        const int2 *pv = sverts + (off_n >> 8);
+        for (int i = lane; i < n; i += 32) { int2 v = pv[i]; W->vx[i] = v.x; W->vy[i] = v.y; }
+        if (lane == 0) { int2 v = pv[0]; W->vx[n] = v.x; W->vy[n] = v.y; }
+        if (P.mode == 2 && lane < 8) {
+            double d = S.dashv[A.view][((size_t)env * MG_MAX_GOALS + P.aux) * 8 + lane];
+            if (lane & 1) W->fy[lane >> 1] = d; else W->fx[lane >> 1] = d;
+        }
+        __syncwarp();
+        {
             if (n <= 8) fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
             else fill_poly_band_edges(W, y0, lane, n, miny, maxy, P.fill);
             __syncwarp();
@@ -484,9 +567,10 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             }
         }
         __syncwarp();
+      }
     }
 
-    if (A.mode == 2) {
+    if (MODE == 2) {
         /* full resolution: surfarray.array3d(...).swapaxes(0, 1) -> u8 [384, 384, 3] (render.py:394-395) */
         uint32_t *dst = (uint32_t *)(A.out + ((size_t)env * RES + y0) * RES * 3);
         for (int g = lane; g < BAND_ROWS * (RES / 4); g += 32) {
@@ -501,22 +585,49 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         return;
     }
 
-    /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block */
-    for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {
-        int oy = o / MG_LORES, ox = o % MG_LORES;
-        const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
-        uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
-        uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
-        uint32_t rgb;
-        if (w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u) rgb = pal[w0 & 31];
-        else rgb = pal_sum16(pal, w0, w1, w2, w3);
-        uint8_t *d = W->lo + o * 3;
-        d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+    /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block.  Blocks of one
+     * palette index (the vast majority) are a table look-up; the mixed ones are queued and summed in a
+     * second, dense pass so that one mixed block does not drag its 31 neighbours through the slow path. */
+    {
+        uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now */
+        const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
+        int n_mixed = 0;
+        for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {       /* 768 = 24 full warps of blocks */
+            int oy = o / MG_LORES, ox = o % MG_LORES;
+            const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
+            uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
+            uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
+            bool mix = !(w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u);
+            unsigned m = __ballot_sync(FULL, mix);
+            uint32_t rgb = pal[w0 & 31];
+            if (mix) {
+                int idx = n_mixed + __popc(m & ((1u << lane) - 1));
+                if (idx < MIXED_MAX) mixed[idx] = (uint16_t)o;
+                else { rgb = pal_sum16(pal, w0, w1, w2, w3); mix = false; }
+            }
+            n_mixed += __popc(m);
+            if (!mix) {
+                uint8_t *d = W->lo + o * 3;
+                d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+            }
+        }
+        __syncwarp();
+        n_mixed = min(n_mixed, MIXED_MAX);
+        for (int k = lane; k < n_mixed; k += 32) {
+            int o = mixed[k];
+            int oy = o / MG_LORES, ox = o % MG_LORES;
+            const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
+            uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
+            uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
+            uint32_t rgb = pal_sum16(pal, w0, w1, w2, w3);
+            uint8_t *d = W->lo + o * 3;
+            d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+        }
     }
     __syncwarp();
 
     const size_t band_off = (size_t)band * LO_BAND_BYTES;
-    if (A.mode == 1) {
+    if (MODE == 1) {
         uint4 *dst = (uint4 *)(A.out + (size_t)env * MG_FRAME_BYTES + band_off);
         for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
         return;
@@ -531,14 +642,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         uint4 *dst = (uint4 *)(ring + (size_t)s * MG_FRAME_BYTES + band_off);
         for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
     }
-    if (!A.obs) return;
+    if (VARIANT == 0) return;
 
     /* fused frame stack: obs[env, 8 rows of this band, 96, 3 * n_groups], channel group g taken from
      * the ring slot the host computed for (view, age).  Frames of this view that are being written
      * by this very launch (age 0, or any age of a fresh env) come from shared memory. */
     const int G = A.n_groups, C = 3 * G;
     uint32_t *obs_w = (uint32_t *)(A.obs + ((size_t)env * MG_LORES * MG_LORES + (size_t)band * LO_ROWS * MG_LORES) * C);
-    if (G == 4) {
+    if (VARIANT == 1) {
         /* LoRes4E / LoRes4A: 4 frames x RGB = 12 bytes per pixel; a lane turns 4 pixels of each frame
          * (3 words each) into 48 contiguous output bytes = three 16-byte stores */
         const uint32_t *srcp[4];
@@ -566,8 +677,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                 dst[half] = make_uint4(o[0], o[1], o[2], o[3]);
             }
         }
-        return;
-    }
+    } else
     for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {      /* q = group of 4 consecutive pixels */
         uint32_t src[MG_MAX_GROUPS][3];
         for (int g = 0; g < G; g++) {
@@ -613,17 +723,34 @@ __global__ void mg_clear_fresh_kernel(MgDeviceState S)
     if (env < S.num_envs) S.istate[mg_field_index(env, I_NF, I_FRESH)] = 0;
 }
 
+void mg_launch_geometry(const MgDeviceState &S, int view, cudaStream_t st)
+{
+    mg_geometry_kernel<<<(S.num_envs + 3) / 4, 128, 0, st>>>(S, view);
+}
+
 static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st)
 {
+    mg_launch_geometry(S, A.view, st);
     static bool attr_set = false;
     size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA;
     if (!attr_set) {
-        cudaFuncSetAttribute(mg_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(mg_render_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(mg_render_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(mg_render_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(mg_render_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(mg_render_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = true;
     }
     long long items = (long long)S.num_envs * N_BANDS;
     int grid = (int)((items + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
-    mg_render_kernel<<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A);
+    int variant = A.mode == 0 ? (!A.obs ? 0 : (A.n_groups == 4 ? 1 : 2)) : A.mode + 2;
+    switch (variant) {
+    case 0: mg_render_kernel<0><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    case 1: mg_render_kernel<1><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    case 2: mg_render_kernel<2><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    case 3: mg_render_kernel<3><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    default: mg_render_kernel<4><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    }
 }
 
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,

@@ -102,4 +102,12 @@ struct MgPrim {
     uint8_t aux;      /* goal index (MG_CHAIN_GOAL) / eye side 0,1 (MG_CHAIN_EYE, MG_CHAIN_PUPIL) */
     uint8_t pad;
 };
+/* screen-space primitive written by mg_geometry_kernel for one view of one env: the rasteriser's bands read
+ * these (16 B, one coalesced load per 32 primitives) instead of redoing the FP64 transform chain per band */
+#define MG_MAX_VERTS 1600      /* per env and view: 15 circles of 100 + polygons; see mg_geometry_kernel */
+struct MgScreenPrim {
+    int off_n;        /* first vertex in the env's vertex pool << 8 | vertex count (0 = culled) */
+    int miny, maxy;   /* truncated vertex rows */
+    uint32_t style;   /* fill | outline << 8 | mode << 16 | aux << 24 */
+};
 enum { MG_CHAIN_CAM = 0, MG_CHAIN_BODY = 1, MG_CHAIN_EYE = 2, MG_CHAIN_PUPIL = 3, MG_CHAIN_GOAL = 4 };

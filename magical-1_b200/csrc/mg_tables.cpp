@@ -120,7 +120,12 @@ int dl_cursor = 0;
 void set_dl(MgTables &T, int id, int n, const vec2 *v)
 {
     T.dl_off[id] = dl_cursor; T.dl_n[id] = n;
-    for (int i = 0; i < n; i++) T.dl_pool[dl_cursor++] = v[i];
+    double rad = 0.0;
+    for (int i = 0; i < n; i++) {
+        T.dl_pool[dl_cursor++] = v[i];
+        rad = std::max(rad, sqrt(v[i].x * v[i].x + v[i].y * v[i].y));
+    }
+    T.dl_rad[id] = rad;
 }
 
 void circle_verts(double radius, vec2 *o) /* render.make_circle, render.py:27-32 */
@@ -296,7 +301,7 @@ MgTables build()
     circle_verts(SHAPE_RAD, tmp); set_dl(T, MG_DL_CIRCLE, MG_CIRCLE_RES, tmp);
     for (int k = 0; k < MG_STAR_PIECES; k++) set_dl(T, MG_DL_STAR_OUT0 + k, sp_n[k], sp_v[k]);
     for (int k = 0; k < MG_STAR_PIECES; k++) set_dl(T, MG_DL_STAR_IN0 + k, spi_n[k], spi_v[k]);
-    T.dl_off[MG_DL_GOAL] = dl_cursor; T.dl_n[MG_DL_GOAL] = 4;
+    T.dl_off[MG_DL_GOAL] = dl_cursor; T.dl_n[MG_DL_GOAL] = 4; T.dl_rad[MG_DL_GOAL] = 0.0;
 
     /* palette (style.py:28-37; entities.py:380-382, 415, 421, 527-528, 717-718, 793-795; base_env.py:199) */
     double grey[3] = { 162 / 255.0, 163 / 255.0, 175 / 255.0 }, c[3];

@@ -1,8 +1,10 @@
 """Join an ncu SASS source page (per-instruction counters) with nvdisasm line info so that instruction
 counts and stall samples can be read per CUDA source line.
-usage: ncu_lines.py <report.ncu-rep> <kernel regex> <cubin.sass from `nvdisasm -g -c`> <function substring>"""
+usage: ncu_lines.py <report.ncu-rep> <kernel regex> <cubin.sass from `nvdisasm -g -c`> <function substring> [N]
+NCU_COL=<column> (e.g. stall_long_sb, stall_no_inst) ranks by that sampling column instead of '# Samples'."""
 import collections
 import csv
+import os
 import re
 import subprocess
 import sys
@@ -13,7 +15,7 @@ out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-n
 rows = list(csv.reader(out.splitlines()))
 hi = [i for i, r in enumerate(rows) if 'Instructions Executed' in r][0]
 hdr = rows[hi]
-ci, si, ai = hdr.index('Instructions Executed'), hdr.index('# Samples'), hdr.index('Address')
+ci, si, ai = hdr.index('Instructions Executed'), hdr.index(os.environ.get('NCU_COL', '# Samples')), hdr.index('Address')
 insts = []
 for r in rows[hi + 1:]:
     try:
