@@ -20,6 +20,7 @@ struct mg_handle {
     bool fused;                 /* single-view HWC stack: composed inside the render kernel */
     int slots[2];               /* newest ring slot per view */
     MgTables *tables_dev;
+    int max_blocks;          /* largest n_blocks ever installed: sizes the step kernel's shared memory */
     mg_scene *scene_stage_dev;  /* [B] staging for mg_set_scenes */
     int32_t *ids_stage_dev;     /* [B] */
     /* mg_step_host staging */
@@ -69,6 +70,7 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     h->cfg = *cfg;
     h->launches = 0; h->timing = 0; h->ms[0] = h->ms[1] = 0; h->timed_launches[0] = h->timed_launches[1] = 0;
     h->slots[0] = h->slots[1] = 0;
+    h->max_blocks = 0;
     memset(&h->S, 0, sizeof(h->S));
     memset(&h->spec, 0, sizeof(h->spec));
     h->spec.n_groups = cfg->n_groups; h->spec.chw = cfg->chw;
@@ -157,6 +159,7 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
             s.task < 0 || s.task >= MG_NUM_TASKS)
             return fail(h, MG_ERR_ARG, "mg_set_scenes: scene out of range");
     }
+    for (int i = 0; i < n; i++) h->max_blocks = scenes_host[i].n_blocks > h->max_blocks ? scenes_host[i].n_blocks : h->max_blocks;
     CK(h, cudaMemcpyAsync(h->scene_stage_dev, scenes_host, (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
     if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, env_ids_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     mg_launch_init(h->S, h->scene_stage_dev, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
@@ -195,7 +198,7 @@ extern "C" int mg_step_physics(mg_handle *h, const int32_t *actions_dev, float *
     cudaStream_t st = (cudaStream_t)stream;
     CK(h, cudaSetDevice(h->cfg.device));
     time_begin(h, 0, st);
-    mg_launch_physics(h->S, actions_dev, reward_dev, done_dev, score_dev, st);
+    mg_launch_physics(h->S, actions_dev, reward_dev, done_dev, score_dev, h->max_blocks, st);
     h->launches++;
     time_end(h, 0, 1, st);
     return check_launch(h, "mg_physics_kernel");
@@ -367,6 +370,8 @@ extern "C" int mg_get_state(mg_handle *h, const int32_t *env_ids_host, int n, vo
 }
 extern "C" int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, const void *blobs_host)
 {
+    /* restored envs may hold any number of blocks */
+    if (h) h->max_blocks = MG_MAX_BLOCKS;
     return state_xfer(h, env_ids_host, n, (unsigned char *)blobs_host, true);
 }
 

@@ -20,7 +20,7 @@
 
 #ifdef __CUDACC__
 #define MG_HD __host__ __device__ __forceinline__
-#define MG_HDN __host__ __device__
+#define MG_HDN __host__ __device__ __noinline__
 #else
 #define MG_HD inline
 #define MG_HDN

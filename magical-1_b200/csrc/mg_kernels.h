@@ -37,7 +37,8 @@ struct MgObsSpec {
 };
 
 void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st);
-void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st);
+/* max_blocks: largest block count of any env in the batch (sizes the per-env shared-memory copy) */
+void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st);
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);
 /* render `view` of every env and push the 96x96 frame into ring slot `slot`; when `fused` is given the
  * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v) */

@@ -17,24 +17,29 @@
  */
 #include <cuda_runtime.h>
 #include <stdlib.h>
+#include <stdio.h>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
 
-struct EnvRef { double *d; int *i; };
+/* d / i: the env's double and int fields up to (not including) the arbiter cache -- HBM, or the step
+ * kernel's shared-memory copy (bodies at d, constraints at dc); da / ia: the env's full field arrays in HBM (arbiters, goals, target) */
+struct EnvRef { double *d; double *dc; int *i; double *da; int *ia; };
 #define DF(e, f) ((e).d[(size_t)(f) * MG_GROUP])
 #define IF(e, f) ((e).i[(size_t)(f) * MG_GROUP])
+#define DGF(e, f) ((e).da[(size_t)(f) * MG_GROUP])
 #define BF(e, b, f) DF(e, D_BODY0 + (b) * B_NF + (f))
-#define CF(e, c, f) DF(e, D_CON0 + (c) * C_NF + (f))
-#define AF(e, a, f) DF(e, D_ARB0 + (a) * A_NF + (f))
-#define ACF(e, a, k, f) DF(e, D_ARB0 + (a) * A_NF + A_CON0 + (k) * AC_NF + (f))
-#define AIF(e, a, f) IF(e, I_ARB0 + (a) * 4 + (f))
+#define CF(e, c, f) ((e).dc[(size_t)((c) * C_NF + (f)) * MG_GROUP])
+#define AF(e, a, f) DGF(e, D_ARB0 + (a) * A_NF + (f))
+#define ACF(e, a, k, f) DGF(e, D_ARB0 + (a) * A_NF + A_CON0 + (k) * AC_NF + (f))
+#define AIF(e, a, f) ((e).ia[(size_t)(I_ARB0 + (a) * 4 + (f)) * MG_GROUP])
 
 __device__ __forceinline__ EnvRef env_ref(double *dstate, int *istate, int env)
 {
     EnvRef e;
-    e.d = dstate + mg_field_index(env, D_NF, 0);
-    e.i = istate + mg_field_index(env, I_NF, 0);
+    e.d = e.da = dstate + mg_field_index(env, D_NF, 0);
+    e.dc = e.d + (size_t)D_CON0 * MG_GROUP;
+    e.i = e.ia = istate + mg_field_index(env, I_NF, 0);
     return e;
 }
 
@@ -203,7 +208,7 @@ __global__ void mg_init_kernel(MgDeviceState S, const mg_scene *scenes, const in
     IF(e, I_TARGET_BLOCK) = sc->target_block; IF(e, I_NVALID) = sc->n_valid_targets;
     IF(e, I_NBODIES) = 1 + MG_RB_COUNT + sc->n_blocks;
     IF(e, I_FRESH) = 1;
-    DF(e, D_TARGET) = sc->target_pos[0]; DF(e, D_TARGET + 1) = sc->target_pos[1];
+    DGF(e, D_TARGET) = sc->target_pos[0]; DGF(e, D_TARGET + 1) = sc->target_pos[1];
     init_body(e, 0, 0, 0, 0, 0.0, 0.0, 0.0);
     MgPrim *prims = S.prims + (size_t)env * MG_MAX_PRIMS;
     int np = 0;
@@ -211,8 +216,8 @@ __global__ void mg_init_kernel(MgDeviceState S, const mg_scene *scenes, const in
     add_prim(prims, &np, MG_DL_ARENA, MG_CHAIN_CAM, 0, MG_PAL_WHITE, MG_PAL_GREY, 1, 0);
     for (int g = 0; g < sc->n_goals; g++) {
         const mg_goal *go = &sc->goals[g];
-        DF(e, D_GOAL0 + g * 4 + 0) = go->cx; DF(e, D_GOAL0 + g * 4 + 1) = go->cy;
-        DF(e, D_GOAL0 + g * 4 + 2) = go->h;  DF(e, D_GOAL0 + g * 4 + 3) = go->w;
+        DGF(e, D_GOAL0 + g * 4 + 0) = go->cx; DGF(e, D_GOAL0 + g * 4 + 1) = go->cy;
+        DGF(e, D_GOAL0 + g * 4 + 2) = go->h;  DGF(e, D_GOAL0 + g * 4 + 3) = go->w;
         IF(e, I_GOAL0 + g) = go->colour | ((go->want_block + 1) << 8);
         add_prim(prims, &np, MG_DL_GOAL, MG_CHAIN_GOAL, 0, MG_PAL_LIGHT0 + go->colour, MG_PAL_COLOUR0 + go->colour, 2, g);
     }
@@ -453,14 +458,34 @@ __device__ __forceinline__ double shape_bound(const MgTables *T, int tpl)
     return T->tpl_bound[tpl];
 }
 
-/* cpSpaceCollideShapes + cpArbiterUpdate for shapes i < j (add order); returns the arbiter slot or -1 */
-__device__ int collide_pair(EnvRef e, int i, int j, int info_i, int info_j, const WShape *Si, const WShape *Sj, int stamp)
+/* l, b, r, t of shape template tpl on a body at p with rotation rot (cpShapeCacheBB), computed in registers:
+ * the same vertex transform as wshape_from_tpl without materialising the shape */
+__device__ __forceinline__ void tpl_world_bb(const MgTables *T, int tpl, vec2 p, vec2 rot, double *bb)
 {
-    int sa = i, sb = j, ia = info_i, ib = info_j;
-    const WShape *A = Si, *B = Sj;
-    if (Si->kind > Sj->kind) { sa = j; sb = i; ia = info_j; ib = info_i; A = Sj; B = Si; }
-    Manifold m;
-    if (collide_shapes(A, B, &m) == 0) return -1;
+    if (tpl >= MG_TPL_WALL0) {
+        int w = tpl - MG_TPL_WALL0;
+        vec2 a = T->wall_a[w], c = T->wall_b[w];
+        bb[0] = fmin(a.x, c.x) - 1.0; bb[1] = fmin(a.y, c.y) - 1.0; bb[2] = fmax(a.x, c.x) + 1.0; bb[3] = fmax(a.y, c.y) + 1.0;
+    } else if (tpl >= MG_TPL_CIRCLE_ROBOT) {
+        double r = tpl == MG_TPL_CIRCLE_ROBOT ? 0.2 : 0.2 * 0.6;
+        bb[0] = p.x - r; bb[1] = p.y - r; bb[2] = p.x + r; bb[3] = p.y + r;
+    } else {
+        const int n = T->tpl_n[tpl];
+        const double r = T->tpl_r[tpl];
+        double l = INFINITY, rr = -INFINITY, bo = INFINITY, t = -INFINITY;
+        for (int i = 0; i < n; i++) {
+            vec2 lv = T->tpl_v[tpl][i];
+            double x = rot.x * lv.x - rot.y * lv.y + p.x, y = rot.y * lv.x + rot.x * lv.y + p.y;
+            l = fmin(l, x); rr = fmax(rr, x); bo = fmin(bo, y); t = fmax(t, y);
+        }
+        bb[0] = l - r; bb[1] = bo - r; bb[2] = rr + r; bb[3] = t + r;
+    }
+}
+
+/* cpArbiterUpdate for the colliding shapes sa, sb (already in cpShapeType order, infos ia, ib) with
+ * manifold m; returns the arbiter slot or -1.  Serial per env: slots are handed out in discovery order. */
+__device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Manifold &m, int stamp)
+{
     int ba = (ia >> 8) & 255, bb = (ib >> 8) & 255;
     int key = sa | (sb << 8);
     int n_arbs = IF(e, I_NARBS), slot = -1;
@@ -573,17 +598,31 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
     for (int f = 0; f < 4; f++) AIF(e, dst, f) = AIF(e, src, f);
 }
 
-/* cpSpaceStep(space, dt) */
-__device__ void space_step(EnvRef e, const MgTables *T)
+
+__device__ unsigned long long mg_dbg_counters[8];
+
+#define PHYS_LANES 16                              /* lanes that share one env in the parallel phases */
+#define PHYS_THREADS 128
+#define PHYS_ENVS (PHYS_THREADS / PHYS_LANES)      /* envs per CTA; lanes 0..PHYS_ENVS-1 of warp 0 run their serial halves */
+
+/* cpSpaceStep(space, dt), first half, one group of PHYS_LANES lanes per env: the phases with independent items (bodies, shape
+ * pairs, pre-steps) spread over the lanes.  Whatever depends on Chipmunk's order runs on one lane in that
+ * order (arbiter cache updates here, the rest in space_step_serial), so the result is the same bit pattern a
+ * serial cpSpaceStep produces.  `order` = shared scratch [MG_NARB + 8]; returns the number of live arbiters. */
+struct NarrowScratch { WShape ws[2]; Manifold mf; };
+
+__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, int dbg)
 {
+    const int gl = lane & (PHYS_LANES - 1);     /* lane within the env's group */
     const double dt = MG_DT;
-    int prev_stamp = IF(e, I_STAMP);
-    int stamp = prev_stamp + 1;
-    IF(e, I_STAMP) = stamp;
+    const int prev_stamp = IF(e, I_STAMP);
+    const int stamp = prev_stamp + 1;
+    __syncwarp(gmask);
 
     /* cpSpaceArbiterSetFilter of the previous step (same effect as running it at the end of
      * that step) merged with this step's arbiter-list reset */
-    {
+    if (gl == 0 && !(dbg & 8)) {
+        IF(e, I_STAMP) = stamp;
         int n_arbs = IF(e, I_NARBS), w = 0;
         for (int q = 0; q < n_arbs; q++) {
             int fl = AIF(e, q, AI_FLAGS);
@@ -599,58 +638,117 @@ __device__ void space_step(EnvRef e, const MgTables *T)
         IF(e, I_NARBS) = w;
     }
 
-    /* cpBodyUpdatePosition for dynamic and kinematic bodies */
-    int nb = IF(e, I_NBODIES);
-    for (int b = 1; b < nb; b++) {
+    /* cpBodyUpdatePosition for dynamic and kinematic bodies: lane = body */
+    const int nb = IF(e, I_NBODIES);
+    for (int b = 1 + gl; b < nb; b += PHYS_LANES) {
         BF(e, b, B_PX) = BF(e, b, B_PX) + (BF(e, b, B_VX) + BF(e, b, B_VBX)) * dt;
         BF(e, b, B_PY) = BF(e, b, B_PY) + (BF(e, b, B_VY) + BF(e, b, B_VBY)) * dt;
         set_angle(e, b, BF(e, b, B_A) + (BF(e, b, B_W) + BF(e, b, B_WB)) * dt);
         BF(e, b, B_VBX) = 0.0; BF(e, b, B_VBY) = 0.0; BF(e, b, B_WB) = 0.0;
     }
+    __syncwarp(gmask);
 
-    /* narrow phase over shape pairs in add order (i < j) */
-    unsigned char order[MG_NARB];
+    /* narrow phase over shape pairs in add order (i < j): for shape i the env's lanes take consecutive j,
+     * run the bounding test and the narrow phase in parallel, then the hits update the arbiter cache one
+     * after the other in j order -- the order a serial double loop discovers them in */
     int n_live = 0;
-    int ns = IF(e, I_NSHAPES);
-    for (int i = 0; i < ns; i++) {
-        int info_i = IF(e, I_SHAPE0 + i);
-        int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
-        vec2 pi = body_p(e, body_i);
-        double ri = shape_bound(T, tpl_i);
-        WShape Si;
-        bool have_i = false;
-        for (int j = i + 1; j < ns; j++) {
-            int info_j = IF(e, I_SHAPE0 + j);
-            int ent_j = info_j >> 16;
-            if (ent_i == ent_j) continue;  /* same body, ShapeFilter group (robot: 1, star pieces), static-static */
-            int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
-            vec2 pj = body_p(e, body_j);
-            double rj = shape_bound(T, tpl_j) + 1e-6;
-            if (tpl_i >= MG_TPL_WALL0) {
-                /* wall i (radius 1) against the bounding circle of shape j */
-                int w = tpl_i - MG_TPL_WALL0;
-                vec2 wa = T->wall_a[w], wb = T->wall_b[w];
-                if (fmin(wa.x, wb.x) - 1.0 > pj.x + rj || fmax(wa.x, wb.x) + 1.0 < pj.x - rj ||
-                    fmin(wa.y, wb.y) - 1.0 > pj.y + rj || fmax(wa.y, wb.y) + 1.0 < pj.y - rj) continue;
-            } else {
-                vec2 d = vsub(pj, pi);
-                double rr = ri + rj;
-                if (vdot(d, d) > rr * rr) continue;
+    const int ns = IF(e, I_NSHAPES);
+    if (!(dbg & 32))
+    for (int i = 0; i + 1 < ns; i++) {
+        const int info_i = IF(e, I_SHAPE0 + i);
+        const int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
+        const vec2 pi = body_p(e, body_i);
+        const double ri = shape_bound(T, tpl_i);
+        for (int j0 = i + 1; j0 < ns; j0 += PHYS_LANES) {
+            const int j = j0 + gl;
+            int info_j = 0;
+            bool cand = false;
+            if (j < ns) {
+                info_j = IF(e, I_SHAPE0 + j);
+                const int ent_j = info_j >> 16;
+                /* same body, ShapeFilter group (robot: 1, star pieces), static-static */
+                cand = ent_i != ent_j;
+                const int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
+                const vec2 pj = body_p(e, body_j);
+                if (cand) {
+                    double rj = shape_bound(T, tpl_j) + 1e-6;
+                    if (tpl_i >= MG_TPL_WALL0) {
+                        /* wall i (radius 1) against the bounding circle of shape j */
+                        int w = tpl_i - MG_TPL_WALL0;
+                        vec2 wa = T->wall_a[w], wb = T->wall_b[w];
+                        if (fmin(wa.x, wb.x) - 1.0 > pj.x + rj || fmax(wa.x, wb.x) + 1.0 < pj.x - rj ||
+                            fmin(wa.y, wb.y) - 1.0 > pj.y + rj || fmax(wa.y, wb.y) + 1.0 < pj.y - rj) cand = false;
+                    } else {
+                        vec2 d = vsub(pj, pi);
+                        double rr = ri + rj;
+                        if (vdot(d, d) > rr * rr) cand = false;
+                    }
+                }
+                if (cand && (dbg & 64)) { atomicAdd(&mg_dbg_counters[1], 1ull); if (tpl_i >= MG_TPL_WALL0) atomicAdd(&mg_dbg_counters[3], 1ull); }
+                if (cand) {
+                    /* bounding boxes (Chipmunk's own broadphase criterion): shapes whose boxes are apart by
+                     * more than rounding noise cannot produce a contact; this needs no shape in memory */
+                    double bi[4], bj[4];
+                    tpl_world_bb(T, tpl_i, pi, body_rot(e, body_i), bi);
+                    tpl_world_bb(T, tpl_j, pj, body_rot(e, body_j), bj);
+                    const double eps = 1e-9;
+                    if (bi[0] > bj[2] + eps || bj[0] > bi[2] + eps || bi[1] > bj[3] + eps || bj[1] > bi[3] + eps) cand = false;
+                }
             }
-            if (!have_i) { wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), &Si); have_i = true; }
-            WShape Sj;
-            wshape_from_tpl(T, tpl_j, pj, body_rot(e, body_j), &Sj);
-            int slot = collide_pair(e, i, j, info_i, info_j, &Si, &Sj, stamp);
-            if (slot >= 0) order[n_live++] = (unsigned char)slot;
+            /* narrow phase + cpArbiterUpdate for the surviving pairs, one after the other in j order (the
+             * order a serial double loop discovers them in).  The shapes live in the env's shared scratch:
+             * per-lane copies would sit in local memory, which has next to no L1 left beside the env state. */
+            unsigned todo = __ballot_sync(gmask, cand && !(dbg & 4));
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                if (lane == src) {
+                    if (dbg & 64) atomicAdd(&mg_dbg_counters[4], 1ull);
+                    const int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
+                    WShape *Si = &scratch->ws[0], *Sj = &scratch->ws[1];
+                    Manifold *m = &scratch->mf;
+                    wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), Si);
+                    wshape_from_tpl(T, tpl_j, body_p(e, body_j), body_rot(e, body_j), Sj);
+                    const bool swapped = Si->kind > Sj->kind;           /* cpSpaceCollideShapes orders by cpShapeType */
+                    const bool hit = (swapped ? collide_shapes(Sj, Si, m) : collide_shapes(Si, Sj, m)) != 0;
+                    int slot = -1;
+                    if (hit) {
+                        if (dbg & 64) atomicAdd(&mg_dbg_counters[2], 1ull);
+                        slot = swapped ? arbiter_update(e, j, i, info_j, info_i, *m, stamp)
+                                       : arbiter_update(e, i, j, info_i, info_j, *m, stamp);
+                    }
+                    order[MG_NARB] = (unsigned char)(slot >= 0);
+                    if (slot >= 0) order[n_live] = (unsigned char)slot;
+                }
+                __syncwarp(gmask);
+                n_live += order[MG_NARB];
+                __syncwarp(gmask);
+            }
         }
     }
 
-    /* pre-step */
+    /* pre-step: arbiters and constraints only write their own fields ... */
     const double slop = 0.01;                       /* base_env.py:207 */
     const double bias_c = T->bias_coef_default;     /* 1 - collision_bias^dt */
-    for (int q = 0; q < n_live; q++) arb_prestep(e, order[q], slop, bias_c);
-    int nc = IF(e, I_NCON);
-    for (int c = 0; c < nc; c++) con_prestep(e, c);
+    const int nc = IF(e, I_NCON);
+    for (int q = gl; q < n_live; q += PHYS_LANES) arb_prestep(e, order[q], slop, bias_c);
+    if (!(dbg & 16))
+    for (int c = gl; c < nc; c += PHYS_LANES)
+        if ((IF(e, I_CON0 + c) & 255) != CON_SPRING) con_prestep(e, c);
+    __syncwarp(gmask);
+    return n_live;
+}
+
+/* the order-dependent rest of cpSpaceStep for one env, run by ONE thread: the spring pre-steps, the cached
+ * impulses and the sequential-impulse iterations.  The step kernel runs this for all envs of a CTA in
+ * neighbouring lanes of one warp, so that the serial chains of several envs share their instruction issue. */
+__device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_live)
+{
+    const int nc = IF(e, I_NCON);
+    /* cpDampedRotarySpring's pre-step applies the spring torque to both bodies: in add order.  No other
+     * pre-step reads angular velocity, so running these after the parallel ones changes nothing. */
+    for (int c = 0; c < nc; c++)
+        if ((IF(e, I_CON0 + c) & 255) == CON_SPRING) con_prestep(e, c);
 
     /* cpBodyUpdateVelocity: gravity 0, damping 1, no forces -> identity */
 
@@ -673,8 +771,8 @@ __device__ __forceinline__ vec2 robot_pos(EnvRef e) { return body_p(e, MG_BODY_R
 /* goal sensor shape: Poly.create_box(body, (w, h)) on a static body at (cx, cy) (entities.py:783-791) */
 __device__ void goal_shape(EnvRef e, int g, WShape *s, double *bb)
 {
-    double cx = DF(e, D_GOAL0 + g * 4 + 0), cy = DF(e, D_GOAL0 + g * 4 + 1);
-    double h = DF(e, D_GOAL0 + g * 4 + 2), w = DF(e, D_GOAL0 + g * 4 + 3);
+    double cx = DGF(e, D_GOAL0 + g * 4 + 0), cy = DGF(e, D_GOAL0 + g * 4 + 1);
+    double h = DGF(e, D_GOAL0 + g * 4 + 2), w = DGF(e, D_GOAL0 + g * 4 + 3);
     double hw = w / 2, hh = h / 2;
     vec2 lv[4] = { V(hw, -hh), V(hw, hh), V(-hw, hh), V(-hw, -hh) };
     s->kind = MG_SHAPE_POLY; s->n = 4; s->r = 0.0;
@@ -884,7 +982,7 @@ __device__ double score_pick_and_place(EnvRef e)                 /* pick_and_pla
     int nv = IF(e, I_NVALID);
     for (int k = 0; k < nv; k++) {
         vec2 sp = block_pos(e, IF(e, I_TARGET_BLOCK));
-        double dx = DF(e, D_TARGET) - sp.x, dy = DF(e, D_TARGET + 1) - sp.y;
+        double dx = DGF(e, D_TARGET) - sp.x, dy = DGF(e, D_TARGET + 1) - sp.y;
         double dist = sqrt(dx * dx + dy * dy);
         double furthest = sqrt(2.0);
         double drange = furthest - SHAPE_RAD;
@@ -926,7 +1024,7 @@ __device__ double env_debug_reward(EnvRef e)
     if (task == MG_TASK_PICK_AND_PLACE) {
         const double SHAPE_RAD = 0.2 * 0.6;
         vec2 sp = block_pos(e, IF(e, I_TARGET_BLOCK));
-        double dx = sp.x - DF(e, D_TARGET), dy = sp.y - DF(e, D_TARGET + 1);
+        double dx = sp.x - DGF(e, D_TARGET), dy = sp.y - DGF(e, D_TARGET + 1);
         double shape_to_target = sqrt(dx * dx + dy * dy);
         double rx = rp.x - sp.x, ry = rp.y - sp.y;
         double robot_to_shape = sqrt(rx * rx + ry * ry);
@@ -939,19 +1037,63 @@ __device__ double env_debug_reward(EnvRef e)
 /* ------------------------------------------------------------------ kernels */
 
 /* BaseEnv.step up to (not including) render */
-__global__ void __launch_bounds__(32) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
-                                                        uint8_t *done_out, float *score_out, int envs_per_warp)
+
+/* the part of one env's state the step touches all the time, in shared memory.  The double block is sized
+ * for the largest env of the batch (max_blocks) so that small scenes leave most of the SM's L1 to the tables
+ * and the arbiter cache: [ (7 + max_blocks) bodies | (10 + 2 max_blocks) constraints ] */
+struct PhysSmemFixed {
+    int i[(I_ARB0 + 3) & ~3];             /* counters, block / goal / constraint / shape infos */
+    unsigned char order[MG_NARB + 8];     /* live arbiter slots in discovery order (+ flag bytes) */
+    NarrowScratch narrow;                 /* the pair of shapes in the narrow phase and their manifold */
+};
+__host__ __device__ inline int phys_smem_doubles(int max_blocks)
 {
-    /* one thread per env, but only envs_per_warp lanes of each warp carry one: an env-step is a long serial,
-     * branchy chain, so fewer envs per warp = less divergence and more warps to hide its latency with */
-    if ((int)threadIdx.x >= envs_per_warp) return;
-    int env = blockIdx.x * envs_per_warp + threadIdx.x;
-    if (env >= S.num_envs) return;
+    /* stride = 1 (mod 16) doubles: the solver lanes of neighbouring envs read the same field of their own
+     * env at the same time, and this keeps those reads on different shared-memory banks */
+    int n = (1 + MG_RB_COUNT + max_blocks) * B_NF + (10 + 2 * max_blocks) * C_NF;
+    return ((n + 15) & ~15) + 1;
+}
+
+__global__ void __launch_bounds__(PHYS_THREADS, 4) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
+                                                                uint8_t *done_out, float *score_out, int max_blocks, int dbg)
+{
+    extern __shared__ __align__(16) unsigned char phys_smem_raw[];
+    const int nd = phys_smem_doubles(max_blocks), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
+    double *smd = (double *)phys_smem_raw;                                     /* [PHYS_ENVS][nd] */
+    PhysSmemFixed *sm = (PhysSmemFixed *)(smd + (size_t)PHYS_ENVS * nd);       /* [PHYS_ENVS] */
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = threadIdx.x / PHYS_LANES, gl = threadIdx.x % PHYS_LANES;
+    const unsigned gmask = (unsigned)((1ull << PHYS_LANES) - 1) << (lane / PHYS_LANES * PHYS_LANES);
+    const int env0 = blockIdx.x * PHYS_ENVS;
+    const int env = env0 + grp;
+    const bool active = env < S.num_envs;       /* idle groups of the last CTA still meet the barriers */
     const MgTables *T = S.tables;
-    EnvRef e = env_ref(S.dstate, S.istate, env);
+    const EnvRef g = env_ref(S.dstate, S.istate, active ? env : env0);
+    PhysSmemFixed *W = &sm[grp];
+    double *Wd = smd + (size_t)grp * nd;
+
+    /* stage the env: ints first (they hold the counts), then the bodies and constraints in use */
+    int nb = 0, nc = 0;
+    if (active) {
+        for (int f = gl; f < I_ARB0; f += PHYS_LANES) W->i[f] = g.i[f];
+        __syncwarp(gmask);
+        nb = W->i[I_NBODIES]; nc = W->i[I_NCON];
+        for (int f = gl; f < nb * B_NF; f += PHYS_LANES) Wd[f] = g.d[D_BODY0 + f];
+        for (int f = gl; f < nc * C_NF; f += PHYS_LANES) Wd[con_off + f] = g.dc[f];
+        __syncwarp(gmask);
+    }
+    EnvRef e;
+    e.d = Wd; e.dc = Wd + con_off; e.i = W->i; e.da = g.da; e.ia = g.ia;
+    /* lane k of warp 0 runs the serial half of the step for env k of this CTA */
+    const bool solver = warp == 0 && lane < PHYS_ENVS && env0 + lane < S.num_envs;
+    EnvRef es = e;
+    if (solver) {
+        const EnvRef gs = env_ref(S.dstate, S.istate, env0 + lane);
+        es.d = smd + (size_t)lane * nd; es.dc = es.d + con_off; es.i = sm[lane].i; es.da = gs.da; es.ia = gs.ia;
+    }
 
     /* ACTION_ID_TO_FLAGS: id = ud + 3 * lr + 9 * grip (entities.py:148-190); Robot.set_action (:435-453) */
-    int action = actions[env];
+    int action = active ? actions[env] : 0;
     action = action < 0 ? 0 : (action >= MG_NUM_ACTIONS ? MG_NUM_ACTIONS - 1 : action);
     int ud = action % 3, lr = (action / 3) % 3, grip = action / 9;
     const double radius = 0.2;
@@ -963,33 +1105,65 @@ __global__ void __launch_bounds__(32) mg_physics_kernel(MgDeviceState S, const i
     double target_finger_angle = grip == 0 ? M_PI / 8 : -0.0;
 
     const int rb = MG_BODY_ROBOT;
-    int motor_l = IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6;  /* robot constraints 0..9: motors are 6 and 9 */
+    const int motor_l = active ? (IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6) : 0;  /* robot constraints 0..9: motors are 6 and 9 */
     for (int sub = 0; sub < 10; sub++) {
-        /* Robot.update (entities.py:455-476) */
-        set_angle(e, rb + MG_RB_CONTROL, BF(e, rb, B_A) + rel_turn_angle);
-        vec2 vel = vrot(body_rot(e, rb), V(0.0, target_speed));
-        BF(e, rb + MG_RB_CONTROL, B_VX) = vel.x; BF(e, rb + MG_RB_CONTROL, B_VY) = vel.y;
-        for (int k = 0; k < 2; k++) {
-            double side = k == 0 ? -1.0 : 1.0;
-            double rel_angle = BF(e, rb + MG_RB_FINGER_L + k, B_A) - BF(e, rb, B_A);
-            double angle_error = rel_angle + side * target_finger_angle;
-            double target_rate = fmax(-1.0, fmin(1.0, angle_error * 10));
-            if (fabs(target_rate) < 1e-4) target_rate = 0.0;
-            CF(e, motor_l + 3 * k, C_P0) = target_rate;
+        if (active) {
+            if (gl == 0) {
+                /* Robot.update (entities.py:455-476) */
+                set_angle(e, rb + MG_RB_CONTROL, BF(e, rb, B_A) + rel_turn_angle);
+                vec2 vel = vrot(body_rot(e, rb), V(0.0, target_speed));
+                BF(e, rb + MG_RB_CONTROL, B_VX) = vel.x; BF(e, rb + MG_RB_CONTROL, B_VY) = vel.y;
+                for (int k = 0; k < 2; k++) {
+                    double side = k == 0 ? -1.0 : 1.0;
+                    double rel_angle = BF(e, rb + MG_RB_FINGER_L + k, B_A) - BF(e, rb, B_A);
+                    double angle_error = rel_angle + side * target_finger_angle;
+                    double target_rate = fmax(-1.0, fmin(1.0, angle_error * 10));
+                    if (fabs(target_rate) < 1e-4) target_rate = 0.0;
+                    CF(e, motor_l + 3 * k, C_P0) = target_rate;
+                }
+            }
+            __syncwarp(gmask);
+            int n_live = (dbg & 2) ? 0 : space_step_parallel(e, T, lane, gmask, W->order, &W->narrow, dbg);
+            if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
         }
-        space_step(e, T);
+        __syncthreads();
+        if (solver && !(dbg & 1)) space_step_serial(es, sm[lane].order, sm[lane].order[MG_NARB + 1]);
+        __syncthreads();
     }
+    if (!active) return;
 
-    int steps = IF(e, I_EPISODE_STEPS) + 1;
-    IF(e, I_EPISODE_STEPS) = steps;
-    bool done = steps >= IF(e, I_HORIZON);
-    double rew = 0.0, eval_score = 0.0;
-    if (done) rew = eval_score = env_score(e, T);
-    if (IF(e, I_DEBUG_REWARD)) rew = env_debug_reward(e);
-    if (reward) reward[env] = (float)rew;
-    if (done_out) done_out[env] = done ? 1 : 0;
-    if (score_out) score_out[env] = (float)eval_score;
-    export_poses(e, S.poses + (size_t)env * MG_POSE_STRIDE);
+    const int steps = IF(e, I_EPISODE_STEPS) + 1;
+    const bool done = steps >= IF(e, I_HORIZON);
+    __syncwarp(gmask);
+    if (gl == 0) IF(e, I_EPISODE_STEPS) = steps;
+    __syncwarp(gmask);
+
+    /* write the env back */
+    for (int f = gl; f < I_ARB0; f += PHYS_LANES) g.i[f] = W->i[f];
+    for (int f = gl; f < nb * B_NF; f += PHYS_LANES) g.d[D_BODY0 + f] = Wd[f];
+    for (int f = gl; f < nc * C_NF; f += PHYS_LANES) g.dc[f] = Wd[con_off + f];
+    /* pose export for the rasteriser and mg_get_bodies: lane = body */
+    double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
+    for (int b = gl; b < MG_NB; b += PHYS_LANES) {
+        double *o = pose + b * MG_POSE_NF;
+        if (b < nb) {
+            o[0] = BF(e, b, B_PX); o[1] = BF(e, b, B_PY); o[2] = BF(e, b, B_A);
+            o[3] = BF(e, b, B_VX); o[4] = BF(e, b, B_VY); o[5] = BF(e, b, B_W);
+            o[6] = BF(e, b, B_RX); o[7] = BF(e, b, B_RY);
+        } else {
+            for (int k = 0; k < MG_POSE_NF; k++) o[k] = 0.0;
+        }
+    }
+    __syncwarp(gmask);
+    if (gl == 0) {
+        /* scores read goals / targets too: use the HBM copy just written */
+        double rew = 0.0, eval_score = 0.0;
+        if (done) rew = eval_score = env_score(g, T);
+        if (IF(e, I_DEBUG_REWARD)) rew = env_debug_reward(g);
+        if (reward) reward[env] = (float)rew;
+        if (done_out) done_out[env] = done ? 1 : 0;
+        if (score_out) score_out[env] = (float)eval_score;
+    }
 }
 
 __global__ void mg_score_kernel(MgDeviceState S, float *out, int debug_reward)
@@ -1024,11 +1198,28 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
     if (n <= 0) return;
     mg_init_kernel<<<(n + 31) / 32, 32, 0, st>>>(S, scenes_dev, env_ids_dev, n);
 }
-void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, cudaStream_t st)
+void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st)
 {
-    static int epw = 0;
-    if (!epw) { const char *v = getenv("MG_PHYS_EPW"); epw = v ? atoi(v) : 8; if (epw < 1 || epw > 32) epw = 8; }
-    mg_physics_kernel<<<(S.num_envs + epw - 1) / epw, 32, 0, st>>>(S, actions, reward, done, score, epw);
+    static size_t attr_set = 0;
+    static int dbg = -1;
+    if (dbg < 0) { const char *v = getenv("MG_PHYS_DEBUG"); dbg = v ? atoi(v) : 0; }
+    if (max_blocks < 0) max_blocks = 0;
+    if (max_blocks > MG_MAX_BLOCKS) max_blocks = MG_MAX_BLOCKS;
+    const size_t smem = ((size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed)) * PHYS_ENVS;
+    if (smem > attr_set) {
+        cudaFuncSetAttribute(mg_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = smem;
+    }
+    mg_physics_kernel<<<(S.num_envs + PHYS_ENVS - 1) / PHYS_ENVS, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks, dbg);
+    if (dbg & 64) {
+        static int calls = 0;
+        if (++calls % 50 == 0) {
+            unsigned long long c[8];
+            cudaMemcpyFromSymbol(c, mg_dbg_counters, sizeof(c));
+            fprintf(stderr, "[mg dbg] launches %d: candidates %llu (wall rows %llu) after bb %llu hits %llu -> per env-substep %.3f cand, %.3f hits\n", calls, c[1], c[3], c[4], c[2],
+                    (double)c[1] / ((double)calls * S.num_envs * 10), (double)c[2] / ((double)calls * S.num_envs * 10));
+        }
+    }
 }
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
 {

@@ -33,7 +33,9 @@
 #define ROW_PARTS (32 / BAND_ROWS)            /* lanes that share one row in the polygon fills */
 #define LO_ROWS (BAND_ROWS / 4)
 #define LO_BAND_BYTES (LO_ROWS * MG_LORES * 3)   /* 2304 */
+#ifndef WARPS_PER_CTA
 #define WARPS_PER_CTA 4
+#endif
 #define FULL 0xffffffffu
 
 struct aff { double a, b, tx, c, d, ty; };   /* 3x3 homogeneous matrix, last row 0 0 1 */

@@ -3,15 +3,15 @@
  *
  * One env = one pymunk Space of the reference (magical/base_env.py:206-226): bodies,
  * constraints in add order, collision shapes in add order, Chipmunk's cached arbiters.
- * Envs are stored in groups of 32, field-major inside a group:
- *     address(env, field) = ((env / 32) * N_FIELDS + field) * 32 + env % 32
- * so the 32 lanes of a warp (one env per lane) read and write 256 contiguous bytes per
- * field.  Doubles and 32-bit ints live in two separate arrays with the same scheme.
+ * One env's fields are contiguous (array of structs): address(env, field) = env * N_FIELDS + field.
+ * The step kernel gives one warp to one env, stages the env's bodies, constraints and shape list in shared
+ * memory with coalesced loads, and leaves the (rarely touched) arbiter cache in HBM.
+ * Doubles and 32-bit ints live in two separate arrays with the same scheme.
  */
 #pragma once
 #include "mg_core.cuh"
 
-#define MG_GROUP 32
+#define MG_GROUP 1   /* envs interleaved per field (1 = array of structs) */
 
 /* body slots: 0 = static body (space.static_body / arena), 1..6 = robot group in
  * Robot.setup add order (MG_RB_*), 7.. = blocks in scene order */

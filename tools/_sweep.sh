@@ -1,0 +1,4 @@
+P='import json,sys; d=json.loads(sys.stdin.read()); print(d["value"], d["ms_per_step"], d["roofline"]["physics_kernel_ms_avg"], d["roofline"]["kernel_ms_avg"])'
+python -m pytest tests/test_gpu_parity.py -m gpu -x -q -s 2>&1 | tail -3
+MG_PHYS_DEBUG=64 python bench.py --steps 100 --warmup 5 --no-cpu-baseline 2>&1 | grep "mg dbg" | tail -1
+python bench.py --steps 60 --warmup 5 --no-cpu-baseline 2>&1 | tail -1 | python -c "$P"
