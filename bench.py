@@ -31,6 +31,10 @@ if ROOT not in sys.path:
 ENV_ID = 'MoveToCorner-Demo-LoRes4E-v0'
 ENVS_PER_GPU = 4096
 OBS_BYTES_PER_ENV = 96 * 96 * 12       # algorithmic bytes written per env-step
+# dram__bytes_read.sum + dram__bytes_write.sum of one mg_render_kernel launch at 4096 envs (ncu --set full,
+# profiles/r1_ncu_summary.txt): 361.9 MB + 546.3 MB; per env it does not depend on the batch size
+NCU_DRAM_BYTES_PER_ENV = (361.917e6 + 546.331e6) / 4096
+NCU_TRAFFIC_SOURCE = 'profiles/r1_ncu_summary.txt (ncu --set full, one launch, 4096 envs), scaled per env'
 METRIC = 'env_steps_per_sec_lores4e'
 UNIT = 'env-steps/s'
 
@@ -289,7 +293,8 @@ def run_gpu(args, rank, world, local_rank):
                        'l2': f'per-step working set (obs {B * OBS_BYTES_PER_ENV / 1e6:.0f} MB + rings + state) exceeds the 126 MB L2',
                        'parallelism': f'env-sharded x{world}, no data-path collective'},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': None, 'kernel': 'mg_render_kernel', 'peak_source': peak_src,
+                         'traffic': B * NCU_DRAM_BYTES_PER_ENV, 'traffic_source': NCU_TRAFFIC_SOURCE,
+                         'kernel': 'mg_render_kernel', 'peak_source': peak_src,
                          'kernel_ms_avg': rend_avg_ms, 'physics_kernel_ms_avg': phys_ms / max(phys_n, 1),
                          'note': 'algorithmic bytes = 110592 B x envs per launch; the kernel is issue/latency-bound, not HBM-bound'},
             'cpu_baseline': cb,

@@ -19,9 +19,11 @@
 #include "../../include/mg_scene.h"
 
 #ifdef __CUDACC__
+#define MG_NOUNROLL _Pragma("unroll 1")
 #define MG_HD __host__ __device__ __forceinline__
 #define MG_HDN __host__ __device__ __noinline__
 #else
+#define MG_NOUNROLL
 #define MG_HD inline
 #define MG_HDN
 #endif
@@ -143,6 +145,7 @@ MG_HD void wshape_from_tpl(const MgTables *T, int tpl, vec2 p, vec2 rot, WShape 
     } else {
         int n = T->tpl_n[tpl];
         s->kind = MG_SHAPE_POLY; s->n = n; s->r = T->tpl_r[tpl];
+        MG_NOUNROLL
         for (int i = 0; i < n; i++) {
             vec2 l = T->tpl_v[tpl][i], m = T->tpl_nrm[tpl][i];
             s->v[i] = V(rot.x * l.x - rot.y * l.y + p.x, rot.y * l.x + rot.x * l.y + p.y);
@@ -212,18 +215,22 @@ MG_HDN inline void convex_axis(const WShape *A, const WShape *B, vec2 *n_out, do
     const double rsum = A->r + B->r;
     double best = -INFINITY;
     vec2 axis = V(1.0, 0.0);
+    MG_NOUNROLL
     for (int i = 0; i < A->n; i++) {
         vec2 fn = face_normal(A, i);
         double sep = INFINITY;
+        MG_NOUNROLL
         for (int j = 0; j < B->n; j++) {
             double s = vdot(vsub(B->v[j], A->v[i]), fn);
             if (s < sep) sep = s;
         }
         if (sep > best) { best = sep; axis = fn; }
     }
+    MG_NOUNROLL
     for (int j = 0; j < B->n; j++) {
         vec2 fn = face_normal(B, j);
         double sep = INFINITY;
+        MG_NOUNROLL
         for (int i = 0; i < A->n; i++) {
             double s = vdot(vsub(A->v[i], B->v[j]), fn);
             if (s < sep) sep = s;
@@ -238,8 +245,10 @@ MG_HDN inline void convex_axis(const WShape *A, const WShape *B, vec2 *n_out, do
     double bestd2 = INFINITY;
     vec2 bn = axis;
     double bd = best;
+    MG_NOUNROLL
     for (int i = 0; i < A->n; i++) {
         vec2 ea = A->v[(i - 1 + A->n) % A->n], eb = A->v[i];
+        MG_NOUNROLL
         for (int j = 0; j < B->n; j++) {
             double t;
             vec2 q = seg_closest(ea, eb, B->v[j], &t);
@@ -256,8 +265,10 @@ MG_HDN inline void convex_axis(const WShape *A, const WShape *B, vec2 *n_out, do
             }
         }
     }
+    MG_NOUNROLL
     for (int j = 0; j < B->n; j++) {
         vec2 ea = B->v[(j - 1 + B->n) % B->n], eb = B->v[j];
+        MG_NOUNROLL
         for (int i = 0; i < A->n; i++) {
             double t;
             vec2 q = seg_closest(ea, eb, A->v[i], &t);
@@ -291,6 +302,7 @@ MG_HD SupEdge support_edge(const WShape *s, vec2 n)
     }
     int count = s->n, i1 = 0;
     double mx = -INFINITY;
+    MG_NOUNROLL
     for (int i = 0; i < count; i++) {
         double d = vdot(s->v[i], n);
         if (d > mx) { mx = d; i1 = i; }
@@ -344,6 +356,7 @@ MG_HDN inline void collide_circle_poly(const WShape *c, const WShape *p, Manifol
     vec2 center = c->v[0];
     int n = p->n;
     double best = -INFINITY; int bi = 0;
+    MG_NOUNROLL
     for (int i = 0; i < n; i++) {
         double s = vdot(vsub(center, p->v[i]), p->nrm[i]);
         if (s > best) { best = s; bi = i; }
@@ -356,6 +369,7 @@ MG_HDN inline void collide_circle_poly(const WShape *c, const WShape *p, Manifol
     } else {
         double bestd2 = INFINITY;
         nrm = vneg(p->nrm[bi]); d = best; pb = center;
+        MG_NOUNROLL
         for (int i = 0; i < n; i++) {
             vec2 ea = p->v[(i - 1 + n) % n], eb = p->v[i];
             double t;

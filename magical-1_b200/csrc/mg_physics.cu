@@ -17,6 +17,7 @@
  */
 #include <cuda_runtime.h>
 #include <stdlib.h>
+#include <stddef.h>
 #include <stdio.h>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
@@ -460,7 +461,7 @@ __device__ __forceinline__ double shape_bound(const MgTables *T, int tpl)
 
 /* l, b, r, t of shape template tpl on a body at p with rotation rot (cpShapeCacheBB), computed in registers:
  * the same vertex transform as wshape_from_tpl without materialising the shape */
-__device__ __forceinline__ void tpl_world_bb(const MgTables *T, int tpl, vec2 p, vec2 rot, double *bb)
+__device__ __noinline__ void tpl_world_bb(const MgTables *T, int tpl, vec2 p, vec2 rot, double *bb)
 {
     if (tpl >= MG_TPL_WALL0) {
         int w = tpl - MG_TPL_WALL0;
@@ -473,6 +474,7 @@ __device__ __forceinline__ void tpl_world_bb(const MgTables *T, int tpl, vec2 p,
         const int n = T->tpl_n[tpl];
         const double r = T->tpl_r[tpl];
         double l = INFINITY, rr = -INFINITY, bo = INFINITY, t = -INFINITY;
+        MG_NOUNROLL
         for (int i = 0; i < n; i++) {
             vec2 lv = T->tpl_v[tpl][i];
             double x = rot.x * lv.x - rot.y * lv.y + p.x, y = rot.y * lv.x + rot.x * lv.y + p.y;
@@ -489,6 +491,7 @@ __device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Ma
     int ba = (ia >> 8) & 255, bb = (ib >> 8) & 255;
     int key = sa | (sb << 8);
     int n_arbs = IF(e, I_NARBS), slot = -1;
+    MG_NOUNROLL
     for (int q = 0; q < n_arbs; q++)
         if ((AIF(e, q, AI_KEY) & 0xffff) == key) { slot = q; break; }
     int state = ARB_FIRST, old_count = 0;
@@ -503,12 +506,15 @@ __device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Ma
         state = fl & 255; old_count = (fl >> 8) & 255;
         uint32_t hh = (uint32_t)AIF(e, slot, AI_HASH);
         old_hash[0] = hh & 0xffff; old_hash[1] = hh >> 16;
+        MG_NOUNROLL
         for (int q = 0; q < old_count; q++) { old_jn[q] = ACF(e, slot, q, AC_JN); old_jt[q] = ACF(e, slot, q, AC_JT); }
     }
     vec2 pa = body_p(e, ba), pb = body_p(e, bb);
+    MG_NOUNROLL
     for (int k = 0; k < m.count; k++) {
         vec2 r1 = vsub(m.p1[k], pa), r2 = vsub(m.p2[k], pb);
         double jn = 0.0, jt = 0.0;
+        MG_NOUNROLL
         for (int q = 0; q < old_count; q++)
             if (m.hash[k] == old_hash[q]) { jn = old_jn[q]; jt = old_jt[q]; }
         ACF(e, slot, k, AC_R1X) = r1.x; ACF(e, slot, k, AC_R1Y) = r1.y;
@@ -532,6 +538,7 @@ __device__ void arb_prestep(EnvRef e, int s, double slop, double bias_c)
     int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
     vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
     vec2 body_delta = vsub(body_p(e, b), body_p(e, a));
+    MG_NOUNROLL
     for (int k = 0; k < count; k++) {
         vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
         ACF(e, s, k, AC_NMASS) = 1.0 / k_scalar(e, a, b, r1, r2, n);
@@ -550,6 +557,7 @@ __device__ void arb_apply_cached(EnvRef e, int s, double dt_coef)
     int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
     int count = (fl >> 8) & 255;
     vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    MG_NOUNROLL
     for (int k = 0; k < count; k++) {
         vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
         vec2 j = vrot(n, V(ACF(e, s, k, AC_JN), ACF(e, s, k, AC_JT)));
@@ -563,6 +571,7 @@ __device__ void arb_apply_impulse(EnvRef e, int s)
     int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
     vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
     double friction = AF(e, s, A_U);
+    MG_NOUNROLL
     for (int k = 0; k < count; k++) {
         double n_mass = ACF(e, s, k, AC_NMASS);
         vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
@@ -594,14 +603,23 @@ __device__ void arb_apply_impulse(EnvRef e, int s)
 
 __device__ void arb_copy(EnvRef e, int dst, int src)
 {
+    MG_NOUNROLL
     for (int f = 0; f < A_NF; f++) AF(e, dst, f) = AF(e, src, f);
+    MG_NOUNROLL
     for (int f = 0; f < 4; f++) AIF(e, dst, f) = AIF(e, src, f);
 }
 
 
-__device__ unsigned long long mg_dbg_counters[8];
-
-#define PHYS_LANES 16                              /* lanes that share one env in the parallel phases */
+#ifndef PHYS_REGSOLVER
+#define PHYS_REGSOLVER 1   /* robot constraints with body velocities in registers */
+#endif
+#ifndef PHYS_BARRIER
+#define PHYS_BARRIER 1     /* serial halves of all envs of a CTA share warp 0 */
+#endif
+#ifndef PHYS_LANES
+#define PHYS_LANES 16
+#endif
+/* PHYS_LANES: lanes that share one env in the parallel phases */
 #define PHYS_THREADS 128
 #define PHYS_ENVS (PHYS_THREADS / PHYS_LANES)      /* envs per CTA; lanes 0..PHYS_ENVS-1 of warp 0 run their serial halves */
 
@@ -609,9 +627,11 @@ __device__ unsigned long long mg_dbg_counters[8];
  * pairs, pre-steps) spread over the lanes.  Whatever depends on Chipmunk's order runs on one lane in that
  * order (arbiter cache updates here, the rest in space_step_serial), so the result is the same bit pattern a
  * serial cpSpaceStep produces.  `order` = shared scratch [MG_NARB + 8]; returns the number of live arbiters. */
-struct NarrowScratch { WShape ws[2]; Manifold mf; };
+#define NARROW_SLOTS 4
+/* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
+struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
 
-__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, int dbg)
+__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch)
 {
     const int gl = lane & (PHYS_LANES - 1);     /* lane within the env's group */
     const double dt = MG_DT;
@@ -621,9 +641,10 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
 
     /* cpSpaceArbiterSetFilter of the previous step (same effect as running it at the end of
      * that step) merged with this step's arbiter-list reset */
-    if (gl == 0 && !(dbg & 8)) {
+    if (gl == 0) {
         IF(e, I_STAMP) = stamp;
         int n_arbs = IF(e, I_NARBS), w = 0;
+        MG_NOUNROLL
         for (int q = 0; q < n_arbs; q++) {
             int fl = AIF(e, q, AI_FLAGS);
             int ticks = prev_stamp - AIF(e, q, AI_STAMP);
@@ -640,6 +661,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
 
     /* cpBodyUpdatePosition for dynamic and kinematic bodies: lane = body */
     const int nb = IF(e, I_NBODIES);
+    MG_NOUNROLL
     for (int b = 1 + gl; b < nb; b += PHYS_LANES) {
         BF(e, b, B_PX) = BF(e, b, B_PX) + (BF(e, b, B_VX) + BF(e, b, B_VBX)) * dt;
         BF(e, b, B_PY) = BF(e, b, B_PY) + (BF(e, b, B_VY) + BF(e, b, B_VBY)) * dt;
@@ -653,12 +675,14 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
      * after the other in j order -- the order a serial double loop discovers them in */
     int n_live = 0;
     const int ns = IF(e, I_NSHAPES);
-    if (!(dbg & 32))
+    MG_NOUNROLL
     for (int i = 0; i + 1 < ns; i++) {
         const int info_i = IF(e, I_SHAPE0 + i);
         const int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
         const vec2 pi = body_p(e, body_i);
         const double ri = shape_bound(T, tpl_i);
+        bool si_built = false;
+        MG_NOUNROLL
         for (int j0 = i + 1; j0 < ns; j0 += PHYS_LANES) {
             const int j = j0 + gl;
             int info_j = 0;
@@ -684,7 +708,6 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
                         if (vdot(d, d) > rr * rr) cand = false;
                     }
                 }
-                if (cand && (dbg & 64)) { atomicAdd(&mg_dbg_counters[1], 1ull); if (tpl_i >= MG_TPL_WALL0) atomicAdd(&mg_dbg_counters[3], 1ull); }
                 if (cand) {
                     /* bounding boxes (Chipmunk's own broadphase criterion): shapes whose boxes are apart by
                      * more than rounding noise cannot produce a contact; this needs no shape in memory */
@@ -695,34 +718,45 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
                     if (bi[0] > bj[2] + eps || bj[0] > bi[2] + eps || bi[1] > bj[3] + eps || bj[1] > bi[3] + eps) cand = false;
                 }
             }
-            /* narrow phase + cpArbiterUpdate for the surviving pairs, one after the other in j order (the
-             * order a serial double loop discovers them in).  The shapes live in the env's shared scratch:
-             * per-lane copies would sit in local memory, which has next to no L1 left beside the env state. */
-            unsigned todo = __ballot_sync(gmask, cand && !(dbg & 4));
+            /* narrow phase for the surviving pairs of this row, up to NARROW_SLOTS at a time on their own
+             * lanes, then cpArbiterUpdate for the hits one after the other in j order (the order a serial
+             * double loop discovers them in).  The shapes live in the env's shared scratch: per-lane copies
+             * would sit in local memory, which has next to no L1 left beside the env state. */
+            unsigned todo = __ballot_sync(gmask, cand);
+            if (todo) {
+                if (lane == __ffs(todo) - 1 && !si_built) wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), &scratch->si);
+                si_built = true;
+                __syncwarp(gmask);
+            }
             while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                if (lane == src) {
-                    if (dbg & 64) atomicAdd(&mg_dbg_counters[4], 1ull);
+                const int rank = __popc(todo & ((1u << lane) - 1));          /* among the pending lanes of this group */
+                const bool mine = cand && ((todo >> lane) & 1) && rank < NARROW_SLOTS;
+                bool hit = false, swapped = false;
+                if (mine) {
                     const int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
-                    WShape *Si = &scratch->ws[0], *Sj = &scratch->ws[1];
-                    Manifold *m = &scratch->mf;
-                    wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), Si);
+                    const WShape *Si = &scratch->si;
+                    WShape *Sj = &scratch->slot[rank].sj;
                     wshape_from_tpl(T, tpl_j, body_p(e, body_j), body_rot(e, body_j), Sj);
-                    const bool swapped = Si->kind > Sj->kind;           /* cpSpaceCollideShapes orders by cpShapeType */
-                    const bool hit = (swapped ? collide_shapes(Sj, Si, m) : collide_shapes(Si, Sj, m)) != 0;
-                    int slot = -1;
-                    if (hit) {
-                        if (dbg & 64) atomicAdd(&mg_dbg_counters[2], 1ull);
-                        slot = swapped ? arbiter_update(e, j, i, info_j, info_i, *m, stamp)
-                                       : arbiter_update(e, i, j, info_i, info_j, *m, stamp);
-                    }
-                    order[MG_NARB] = (unsigned char)(slot >= 0);
-                    if (slot >= 0) order[n_live] = (unsigned char)slot;
+                    swapped = Si->kind > Sj->kind;           /* cpSpaceCollideShapes orders by cpShapeType */
+                    hit = (swapped ? collide_shapes(Sj, Si, &scratch->slot[rank].mf) : collide_shapes(Si, Sj, &scratch->slot[rank].mf)) != 0;
                 }
-                __syncwarp(gmask);
-                n_live += order[MG_NARB];
-                __syncwarp(gmask);
+                unsigned hits = __ballot_sync(gmask, hit);
+                while (hits) {
+                    const int src = __ffs(hits) - 1;
+                    hits &= hits - 1;
+                    if (lane == src) {
+                        const Manifold &m = scratch->slot[rank].mf;
+                        int slot = swapped ? arbiter_update(e, j, i, info_j, info_i, m, stamp)
+                                           : arbiter_update(e, i, j, info_i, info_j, m, stamp);
+                        order[MG_NARB] = (unsigned char)(slot >= 0);
+                        if (slot >= 0) order[n_live] = (unsigned char)slot;
+                    }
+                    __syncwarp(gmask);
+                    n_live += order[MG_NARB];
+                    __syncwarp(gmask);
+                }
+                /* retire the lanes that ran */
+                todo &= ~__ballot_sync(gmask, mine);
             }
         }
     }
@@ -731,12 +765,139 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
     const double slop = 0.01;                       /* base_env.py:207 */
     const double bias_c = T->bias_coef_default;     /* 1 - collision_bias^dt */
     const int nc = IF(e, I_NCON);
+    MG_NOUNROLL
     for (int q = gl; q < n_live; q += PHYS_LANES) arb_prestep(e, order[q], slop, bias_c);
-    if (!(dbg & 16))
+    MG_NOUNROLL
     for (int c = gl; c < nc; c += PHYS_LANES)
         if ((IF(e, I_CON0 + c) & 255) != CON_SPRING) con_prestep(e, c);
     __syncwarp(gmask);
     return n_live;
+}
+
+/* ---- the robot's ten constraints with the six robot bodies' velocities in registers.
+ * Robot.setup adds them in a fixed order on fixed bodies (entities.py:238-372), so inside the iteration loop
+ * their body operands can be registers instead of shared-memory round trips, and with no stores to body
+ * memory in between the compiler is free to load the next constraint's coefficients early.  Every formula is
+ * the one in con_apply_impulse, operation for operation. */
+struct BodyV { double vx, vy, w, minv, iinv; };
+
+template <int B>
+__device__ __forceinline__ void reg_apply_impulse(BodyV (&r)[MG_RB_COUNT], vec2 j, vec2 rr)
+{
+    r[B].vx = r[B].vx + j.x * r[B].minv;
+    r[B].vy = r[B].vy + j.y * r[B].minv;
+    r[B].w = r[B].w + r[B].iinv * vcross(rr, j);
+}
+
+template <int A, int B>
+__device__ __forceinline__ void reg_pivot(BodyV (&r)[MG_RB_COUNT], double *cf)
+{
+    const double j_max = cf[C_JMAX];
+    vec2 r1 = V(cf[C_R1X], cf[C_R1Y]), r2 = V(cf[C_R2X], cf[C_R2Y]);
+    vec2 v1 = vadd(V(r[A].vx, r[A].vy), vmul(vperp(r1), r[A].w));
+    vec2 v2 = vadd(V(r[B].vx, r[B].vy), vmul(vperp(r2), r[B].w));
+    vec2 vr = vsub(v2, v1);
+    vec2 d = vsub(V(cf[C_BIASX], cf[C_BIASY]), vr);
+    vec2 j = V(d.x * cf[C_K0] + d.y * cf[C_K1], d.x * cf[C_K2] + d.y * cf[C_K3]);
+    vec2 j_old = V(cf[C_JX], cf[C_JY]);
+    vec2 j_acc = vclamp_len(vadd(j_old, j), j_max);
+    cf[C_JX] = j_acc.x; cf[C_JY] = j_acc.y;
+    vec2 dj = vsub(j_acc, j_old);
+    reg_apply_impulse<A>(r, vneg(dj), r1);
+    reg_apply_impulse<B>(r, dj, r2);
+}
+
+template <int A, int B>
+__device__ __forceinline__ void reg_gear(BodyV (&r)[MG_RB_COUNT], double *cf)
+{
+    const double j_max = cf[C_JMAX];
+    double ratio = cf[C_P1];
+    double wr = r[B].w * ratio - r[A].w;
+    double j = (cf[C_BIASX] - wr) * cf[C_ISUM];
+    double j_old = cf[C_JX];
+    double j_acc = dclamp(j_old + j, -j_max, j_max);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * r[A].iinv * (1.0 / ratio);
+    r[B].w = r[B].w + j * r[B].iinv;
+}
+
+template <int A, int B>
+__device__ __forceinline__ void reg_spring(BodyV (&r)[MG_RB_COUNT], double *cf)
+{
+    double wrn = r[A].w - r[B].w;
+    double w_damp = (cf[C_BIASY] - wrn) * cf[C_P0];
+    cf[C_BIASY] = wrn + w_damp;
+    double j_damp = w_damp * cf[C_ISUM];
+    cf[C_JX] = cf[C_JX] + j_damp;
+    r[A].w = r[A].w + j_damp * r[A].iinv;
+    r[B].w = r[B].w - j_damp * r[B].iinv;
+}
+
+template <int A, int B>
+__device__ __forceinline__ void reg_limit(BodyV (&r)[MG_RB_COUNT], double *cf)
+{
+    const double j_max = cf[C_JMAX];
+    double bias = cf[C_BIASX];
+    if (!bias) return;
+    double wr = r[B].w - r[A].w;
+    double j = -(bias + wr) * cf[C_ISUM];
+    double j_old = cf[C_JX], j_acc;
+    if (bias < 0.0) j_acc = dclamp(j_old + j, 0.0, j_max);
+    else j_acc = dclamp(j_old + j, -j_max, 0.0);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * r[A].iinv;
+    r[B].w = r[B].w + j * r[B].iinv;
+}
+
+template <int A, int B>
+__device__ __forceinline__ void reg_motor(BodyV (&r)[MG_RB_COUNT], double *cf)
+{
+    const double j_max = cf[C_JMAX];
+    double wr = r[B].w - r[A].w + cf[C_P0];
+    double j = -wr * cf[C_ISUM];
+    double j_old = cf[C_JX];
+    double j_acc = dclamp(j_old + j, -j_max, j_max);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * r[A].iinv;
+    r[B].w = r[B].w + j * r[B].iinv;
+}
+
+/* one sequential-impulse pass over the robot's constraints c0 .. c0+9 (add order of setup_robot) */
+__device__ __forceinline__ void robot_constraints_pass(BodyV (&r)[MG_RB_COUNT], double *cf0)
+{
+    reg_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 0 * C_NF);
+    reg_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 1 * C_NF);
+    reg_spring<MG_RB_ROBOT, MG_RB_PUPIL_L>(r, cf0 + 2 * C_NF);
+    reg_spring<MG_RB_ROBOT, MG_RB_PUPIL_R>(r, cf0 + 3 * C_NF);
+    reg_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 4 * C_NF);
+    reg_limit<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 5 * C_NF);
+    reg_motor<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 6 * C_NF);
+    reg_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 7 * C_NF);
+    reg_limit<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 8 * C_NF);
+    reg_motor<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF);
+}
+
+__device__ __forceinline__ void robot_regs_load(EnvRef e, BodyV (&r)[MG_RB_COUNT])
+{
+#pragma unroll
+    MG_NOUNROLL
+    for (int k = 0; k < MG_RB_COUNT; k++) {
+        const int b = MG_BODY_ROBOT + k;
+        r[k].vx = BF(e, b, B_VX); r[k].vy = BF(e, b, B_VY); r[k].w = BF(e, b, B_W);
+        r[k].minv = BF(e, b, B_MINV); r[k].iinv = BF(e, b, B_IINV);
+    }
+}
+__device__ __forceinline__ void robot_regs_store(EnvRef e, const BodyV (&r)[MG_RB_COUNT])
+{
+#pragma unroll
+    MG_NOUNROLL
+    for (int k = 0; k < MG_RB_COUNT; k++) {
+        const int b = MG_BODY_ROBOT + k;
+        BF(e, b, B_VX) = r[k].vx; BF(e, b, B_VY) = r[k].vy; BF(e, b, B_W) = r[k].w;
+    }
 }
 
 /* the order-dependent rest of cpSpaceStep for one env, run by ONE thread: the spring pre-steps, the cached
@@ -747,6 +908,7 @@ __device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_li
     const int nc = IF(e, I_NCON);
     /* cpDampedRotarySpring's pre-step applies the spring torque to both bodies: in add order.  No other
      * pre-step reads angular velocity, so running these after the parallel ones changes nothing. */
+    MG_NOUNROLL
     for (int c = 0; c < nc; c++)
         if ((IF(e, I_CON0 + c) & 255) == CON_SPRING) con_prestep(e, c);
 
@@ -754,13 +916,43 @@ __device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_li
 
     double dt_coef = IF(e, I_STEPPED) ? 1.0 : 0.0;  /* prev_dt == 0 ? 0 : dt / prev_dt */
     IF(e, I_STEPPED) = 1;
+    MG_NOUNROLL
     for (int q = 0; q < n_live; q++) arb_apply_cached(e, order[q], dt_coef);
+    MG_NOUNROLL
     for (int c = 0; c < nc; c++) con_apply_cached(e, c, dt_coef);
 
+#if PHYS_REGSOLVER
+    /* constraints in add order: the robot's ten sit at c_robot, the blocks' pairs before or after them
+     * (BaseEnv.add_entities order, I_ROBOT_FIRST); block constraints only touch the static body and a block */
+    const int c_robot = IF(e, I_ROBOT_FIRST) ? 0 : nc - 10;
+    double *cf_robot = e.dc + (size_t)c_robot * C_NF;
+    BodyV r[MG_RB_COUNT];
+    robot_regs_load(e, r);
+    MG_NOUNROLL
     for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
+        if (n_live) {
+            /* contacts may involve any body: give them the current velocities and take theirs back */
+            robot_regs_store(e, r);
+            MG_NOUNROLL
+            for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order[q]);
+            robot_regs_load(e, r);
+        }
+        MG_NOUNROLL
+        for (int c = 0; c < c_robot; c++) con_apply_impulse(e, c);
+        robot_constraints_pass(r, cf_robot);
+        MG_NOUNROLL
+        for (int c = c_robot + 10; c < nc; c++) con_apply_impulse(e, c);
+    }
+    robot_regs_store(e, r);
+#else
+    MG_NOUNROLL
+    for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
+        MG_NOUNROLL
         for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order[q]);
+        MG_NOUNROLL
         for (int c = 0; c < nc; c++) con_apply_impulse(e, c);
     }
+#endif
 }
 
 /* ------------------------------------------------------------------ scores (magical/benchmarks/*.py score_on_end_of_traj) */
@@ -991,7 +1183,7 @@ __device__ double score_pick_and_place(EnvRef e)                 /* pick_and_pla
     return best;
 }
 
-__device__ double env_score(EnvRef e, const MgTables *T)
+__device__ __noinline__ double env_score(EnvRef e, const MgTables *T)
 {
     switch (IF(e, I_TASK)) {
     case MG_TASK_MOVE_TO_CORNER: return score_move_to_corner(e);
@@ -1008,7 +1200,7 @@ __device__ double env_score(EnvRef e, const MgTables *T)
 }
 
 /* move_to_corner.py:86-100, pick_and_place.py:114-124 */
-__device__ double env_debug_reward(EnvRef e)
+__device__ __noinline__ double env_debug_reward(EnvRef e)
 {
     vec2 rp = robot_pos(e);
     int task = IF(e, I_TASK);
@@ -1046,6 +1238,8 @@ struct PhysSmemFixed {
     unsigned char order[MG_NARB + 8];     /* live arbiter slots in discovery order (+ flag bytes) */
     NarrowScratch narrow;                 /* the pair of shapes in the narrow phase and their manifold */
 };
+#define PHYS_TABLE_BYTES ((int)((offsetof(MgTables, dl_off) + 15) & ~15))
+
 __host__ __device__ inline int phys_smem_doubles(int max_blocks)
 {
     /* stride = 1 (mod 16) doubles: the solver lanes of neighbouring envs read the same field of their own
@@ -1055,21 +1249,29 @@ __host__ __device__ inline int phys_smem_doubles(int max_blocks)
 }
 
 __global__ void __launch_bounds__(PHYS_THREADS, 4) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
-                                                                uint8_t *done_out, float *score_out, int max_blocks, int dbg)
+                                                                uint8_t *done_out, float *score_out, int max_blocks)
 {
     extern __shared__ __align__(16) unsigned char phys_smem_raw[];
     const int nd = phys_smem_doubles(max_blocks), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
-    double *smd = (double *)phys_smem_raw;                                     /* [PHYS_ENVS][nd] */
+    /* the collision half of the tables (templates, walls, constants) in shared memory: with the env state
+     * resident there is little L1 left, and every table read from HBM/L2 is a ~700-cycle stall on a serial path */
+    {
+        const double *src = (const double *)S.tables;
+        double *dst = (double *)phys_smem_raw;
+        for (int k = threadIdx.x; k < PHYS_TABLE_BYTES / 8; k += PHYS_THREADS) dst[k] = src[k];
+    }
+    double *smd = (double *)(phys_smem_raw + PHYS_TABLE_BYTES);                /* [PHYS_ENVS][nd] */
     PhysSmemFixed *sm = (PhysSmemFixed *)(smd + (size_t)PHYS_ENVS * nd);       /* [PHYS_ENVS] */
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31;
     const int grp = threadIdx.x / PHYS_LANES, gl = threadIdx.x % PHYS_LANES;
     const unsigned gmask = (unsigned)((1ull << PHYS_LANES) - 1) << (lane / PHYS_LANES * PHYS_LANES);
     const int env0 = blockIdx.x * PHYS_ENVS;
     const int env = env0 + grp;
     const bool active = env < S.num_envs;       /* idle groups of the last CTA still meet the barriers */
-    const MgTables *T = S.tables;
+    const MgTables *T = (const MgTables *)phys_smem_raw;   /* only the fields before dl_off are valid */
     const EnvRef g = env_ref(S.dstate, S.istate, active ? env : env0);
     PhysSmemFixed *W = &sm[grp];
+    __syncthreads();
     double *Wd = smd + (size_t)grp * nd;
 
     /* stage the env: ints first (they hold the counts), then the bodies and constraints in use */
@@ -1084,14 +1286,15 @@ __global__ void __launch_bounds__(PHYS_THREADS, 4) mg_physics_kernel(MgDeviceSta
     }
     EnvRef e;
     e.d = Wd; e.dc = Wd + con_off; e.i = W->i; e.da = g.da; e.ia = g.ia;
+#if PHYS_BARRIER
     /* lane k of warp 0 runs the serial half of the step for env k of this CTA */
-    const bool solver = warp == 0 && lane < PHYS_ENVS && env0 + lane < S.num_envs;
+    const bool solver = threadIdx.x < PHYS_ENVS && env0 + lane < S.num_envs;
     EnvRef es = e;
     if (solver) {
         const EnvRef gs = env_ref(S.dstate, S.istate, env0 + lane);
         es.d = smd + (size_t)lane * nd; es.dc = es.d + con_off; es.i = sm[lane].i; es.da = gs.da; es.ia = gs.ia;
     }
-
+#endif
     /* ACTION_ID_TO_FLAGS: id = ud + 3 * lr + 9 * grip (entities.py:148-190); Robot.set_action (:435-453) */
     int action = active ? actions[env] : 0;
     action = action < 0 ? 0 : (action >= MG_NUM_ACTIONS ? MG_NUM_ACTIONS - 1 : action);
@@ -1123,12 +1326,22 @@ __global__ void __launch_bounds__(PHYS_THREADS, 4) mg_physics_kernel(MgDeviceSta
                 }
             }
             __syncwarp(gmask);
-            int n_live = (dbg & 2) ? 0 : space_step_parallel(e, T, lane, gmask, W->order, &W->narrow, dbg);
+            int n_live = space_step_parallel(e, T, lane, gmask, W->order, &W->narrow);
             if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
         }
+#if PHYS_BARRIER
+        /* the order-dependent halves of all envs of the CTA in neighbouring lanes of warp 0: their serial
+         * chains then cost one instruction stream instead of PHYS_ENVS */
         __syncthreads();
-        if (solver && !(dbg & 1)) space_step_serial(es, sm[lane].order, sm[lane].order[MG_NARB + 1]);
+        if (solver) space_step_serial(es, sm[lane].order, sm[lane].order[MG_NARB + 1]);
         __syncthreads();
+#else
+        if (active) {
+            /* the order-dependent half on the group's first lane; groups never wait for each other */
+            if (gl == 0) space_step_serial(e, W->order, W->order[MG_NARB + 1]);
+            __syncwarp(gmask);
+        }
+#endif
     }
     if (!active) return;
 
@@ -1201,25 +1414,14 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st)
 {
     static size_t attr_set = 0;
-    static int dbg = -1;
-    if (dbg < 0) { const char *v = getenv("MG_PHYS_DEBUG"); dbg = v ? atoi(v) : 0; }
     if (max_blocks < 0) max_blocks = 0;
     if (max_blocks > MG_MAX_BLOCKS) max_blocks = MG_MAX_BLOCKS;
-    const size_t smem = ((size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed)) * PHYS_ENVS;
+    const size_t smem = PHYS_TABLE_BYTES + ((size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed)) * PHYS_ENVS;
     if (smem > attr_set) {
         cudaFuncSetAttribute(mg_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = smem;
     }
-    mg_physics_kernel<<<(S.num_envs + PHYS_ENVS - 1) / PHYS_ENVS, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks, dbg);
-    if (dbg & 64) {
-        static int calls = 0;
-        if (++calls % 50 == 0) {
-            unsigned long long c[8];
-            cudaMemcpyFromSymbol(c, mg_dbg_counters, sizeof(c));
-            fprintf(stderr, "[mg dbg] launches %d: candidates %llu (wall rows %llu) after bb %llu hits %llu -> per env-substep %.3f cand, %.3f hits\n", calls, c[1], c[3], c[4], c[2],
-                    (double)c[1] / ((double)calls * S.num_envs * 10), (double)c[2] / ((double)calls * S.num_envs * 10));
-        }
-    }
+    mg_physics_kernel<<<(S.num_envs + PHYS_ENVS - 1) / PHYS_ENVS, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks);
 }
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
 {
