@@ -131,7 +131,7 @@ def cpu_baseline(n_threads, seconds_target=12.0):
     dt = time.perf_counter() - t0
     rate = n_envs * steps / dt
     # scale the sample so that the measured run lasts about `seconds_target`
-    steps2 = int(max(20, min(400, steps * seconds_target / max(dt, 1e-3))))
+    steps2 = int(max(20, min(6000, steps * seconds_target / max(dt, 1e-3))))
     actions = np.ascontiguousarray(np.random.RandomState(1234).randint(0, 18, size=(steps2, n_envs)), np.int32)
     t0 = time.perf_counter()
     lib.orc_bench_rollout(scenes, n_envs, steps2, actions.ctypes.data, n_threads, 1, C.byref(ck))
