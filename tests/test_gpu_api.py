@@ -306,3 +306,50 @@ def test_full_size_batch_properties(orc):
         one = solo.step(actions[t, 1234:1235])[0]['past_obs']
     np.testing.assert_array_equal(one.cpu().numpy()[0], host[1234])
     solo.close()
+
+
+@pytest.mark.parametrize('env_id,n_envs,n_unique', [
+    ('FindDupe-TestLayout-LoRes4E-v0', 16384, 256),      # BASELINE.json configs[2]
+    ('ClusterColour-TestAll-LoRes4E-v0', 32768, 256),    # BASELINE.json configs[3] (CountPlus, max block count)
+])
+def test_large_batches_tile_consistently(orc, env_id, n_envs, n_unique):
+    """BASELINE configs[2] / [3] sizes.  The batch is n_unique host-sampled scenes tiled to n_envs, so every
+    copy of a scene must produce bit-identical observations, rewards and poses wherever it sits in the batch
+    (size-independent property), and a sample of the unique scenes is checked against the oracle."""
+    import magical_b200 as m
+    from magical_b200 import tasks
+    sp = m.spec(env_id)
+    kw = {k: v for k, v in sp['kwargs'].items() if k not in ('res_hw', 'fps', 'phys_steps', 'phys_iter', 'max_episode_steps')}
+    rand_dynamics = kw.pop('rand_dynamics', False)
+    uniq = []
+    seed = 0
+    while len(uniq) < n_unique:
+        try:
+            uniq.append(tasks.sample_scene(sp['entry_point'], np.random.RandomState(1000 + seed), sp['max_episode_steps'],
+                                           rand_dynamics=rand_dynamics, **kw))
+        except tasks.PlacementError:
+            pass
+        seed += 1
+    scenes = [uniq[i % n_unique] for i in range(n_envs)]
+    env = m.make(env_id, num_envs=n_envs, seed=0, obs_keys=('past_obs',))
+    env.auto_reset = False
+    env.reset(scenes)
+    T = 6
+    act_u = np.random.RandomState(9).randint(0, 18, size=(T, n_unique))
+    actions = np.tile(act_u, (1, n_envs // n_unique))
+    check = list(range(0, n_unique, n_unique // 8))
+    oracles = {i: orc.Env(to_oracle_scene(orc, uniq[i])) for i in check}
+    for t in range(T):
+        obs, rew, done, info = env.step(actions[t])
+        for i, o in oracles.items():
+            o.step(int(act_u[t, i]))
+    past = obs['past_obs'].view(n_envs // n_unique, n_unique, 96, 96, 12)
+    assert bool((past == past[0:1]).all().item())
+    bodies = env.get_bodies().reshape(n_envs // n_unique, n_unique, -1)
+    assert (bodies == bodies[0:1]).all()
+    host = past[0].cpu().numpy()
+    got = env.get_bodies()
+    for i, o in oracles.items():
+        assert np.abs(got[i, :o.n_bodies, :3] - o.bodies()[:, :3]).max() <= 1e-3, i
+        assert _close(host[i][..., 9:], orc.downsample4(o.render(_E))), i
+    env.close()
