@@ -620,7 +620,9 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 #define PHYS_LANES 16
 #endif
 /* PHYS_LANES: lanes that share one env in the parallel phases */
-#define PHYS_THREADS 128
+#ifndef PHYS_THREADS
+#define PHYS_THREADS 256
+#endif
 #define PHYS_ENVS (PHYS_THREADS / PHYS_LANES)      /* envs per CTA; lanes 0..PHYS_ENVS-1 of warp 0 run their serial halves */
 
 /* cpSpaceStep(space, dt), first half, one group of PHYS_LANES lanes per env: the phases with independent items (bodies, shape
@@ -1248,7 +1250,7 @@ __host__ __device__ inline int phys_smem_doubles(int max_blocks)
     return ((n + 15) & ~15) + 1;
 }
 
-__global__ void __launch_bounds__(PHYS_THREADS, 4) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
+__global__ void __launch_bounds__(PHYS_THREADS, 512 / PHYS_THREADS) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
                                                                 uint8_t *done_out, float *score_out, int max_blocks)
 {
     extern __shared__ __align__(16) unsigned char phys_smem_raw[];

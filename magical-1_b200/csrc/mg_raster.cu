@@ -29,7 +29,8 @@
 #define BAND_ROWS 32
 #endif
 #define N_BANDS (RES / BAND_ROWS)
-#define ROW_STRIDE 388                       /* 97 words: lane-per-row word stores are bank-conflict free */
+#define ROW_STRIDE 400                       /* 25 x 16 B: rows are 16-byte aligned and the 16-byte stores of a quarter
+                                              * warp (8 lanes = 8 rows, 100 words apart) fall on distinct banks */
 #define ROW_PARTS (32 / BAND_ROWS)            /* lanes that share one row in the polygon fills */
 #define LO_ROWS (BAND_ROWS / 4)
 #define LO_BAND_BYTES (LO_ROWS * MG_LORES * 3)   /* 2304 */
@@ -94,7 +95,7 @@ __device__ aff ego_camera(double cx, double cy, double cs, double sn)
 }
 
 struct WarpSmem {
-    uint8_t buf[BAND_ROWS * ROW_STRIDE];     /* palette indices of the band */
+    alignas(16) uint8_t buf[BAND_ROWS * ROW_STRIDE];     /* palette indices of the band */
     int vx[MG_CIRCLE_RES + 4], vy[MG_CIRCLE_RES + 4];
     double fx[4], fy[4];                     /* float vertices (dashed outlines only) */
     uint8_t lo[LO_BAND_BYTES];               /* downsampled band, HWC */
@@ -270,9 +271,12 @@ __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t 
         lo = a; hi = part == ROW_PARTS - 1 ? hi : min(hi, b - 1);
         if (lo > hi) return;
     }
-    uint32_t c4 = c * 0x01010101u;
+    const uint32_t c4 = c * 0x01010101u;
     int x = lo;
     while (x <= hi && (x & 3)) row[x++] = c;
+    while (x + 3 <= hi && (x & 15)) { *(uint32_t *)(row + x) = c4; x += 4; }
+    const uint4 c16 = make_uint4(c4, c4, c4, c4);
+    for (; x + 15 <= hi; x += 16) *(uint4 *)(row + x) = c16;
     for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
     for (; x <= hi; x++) row[x] = c;
 }
@@ -501,7 +505,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
 
     /* the fused stack reads three older frames of this band from the ring at the very end: start pulling
      * their lines towards L2 now (18 lines of 128 B per frame band) */
-    if (VARIANT >= 1 && VARIANT <= 2 && lane < LO_BAND_BYTES / 128) {
+    if (VARIANT == 2 && lane < LO_BAND_BYTES / 128) {
 #pragma unroll
         for (int g = 0; g < MG_MAX_GROUPS; g++) {
             if (g >= A.n_groups || (A.gview[g] == A.view && A.gage[g] == 0)) continue;
@@ -511,7 +515,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         }
     }
     /* Viewer._clear: background */
-    for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 4; i += 32) ((uint32_t *)W->buf)[i] = MG_PAL_BG * 0x01010101u;
+    {
+        const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
+        const uint4 bg16 = make_uint4(bg4, bg4, bg4, bg4);
+        for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 16; i += 32) ((uint4 *)W->buf)[i] = bg16;
+    }
     __syncwarp();
 
     /* primitives in draw order, 32 headers per coalesced load; each lane tests its own primitive against
@@ -587,6 +595,30 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         return;
     }
 
+    /* 4-group stack: the three older frames of this band are needed at the very end; load them into
+     * registers now so that their HBM/L2 latency hides behind the downsample (54 words per lane) */
+    constexpr int PRE_IT = LO_ROWS * MG_LORES / 4 / 32;
+    uint32_t pre[VARIANT == 1 ? PRE_IT : 1][3][3];
+    bool fresh = false, use_pre = false;
+    if (MODE == 0) fresh = S.istate[mg_field_index(env, I_NF, I_FRESH)] != 0;
+    if (VARIANT == 1) {
+        use_pre = !fresh && A.gview[3] == A.view && A.gage[3] == 0;
+#pragma unroll
+        for (int g = 0; g < 3; g++) use_pre = use_pre && !(A.gview[g] == A.view && A.gage[g] == 0);
+        if (use_pre) {
+#pragma unroll
+            for (int g = 0; g < 3; g++) {
+                const uint32_t *p = (const uint32_t *)(S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES
+                                                       + (size_t)band * LO_BAND_BYTES);
+#pragma unroll
+                for (int it = 0; it < PRE_IT; it++) {
+                    const int q = lane + 32 * it;
+                    pre[it][g][0] = __ldg(p + q * 3); pre[it][g][1] = __ldg(p + q * 3 + 1); pre[it][g][2] = __ldg(p + q * 3 + 2);
+                }
+            }
+        }
+    }
+
     /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block.  Blocks of one
      * palette index (the vast majority) are a table look-up; the mixed ones are queued and summed in a
      * second, dense pass so that one mixed block does not drag its 31 neighbours through the slow path. */
@@ -637,7 +669,6 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
 
     /* mode 0: push into the frame ring.  A freshly reset env fills every slot with its first
      * frame (FlattenFrameStack.reset / EagerDictFrameStack.reset, benchmarks/__init__.py:66-74, 139-147) */
-    const bool fresh = S.istate[mg_field_index(env, I_NF, I_FRESH)] != 0;
     uint8_t *ring = S.ring[A.view] + (size_t)env * MG_MAX_RING * MG_FRAME_BYTES;
     for (int s = 0; s < MG_MAX_RING; s++) {
         if (!fresh && s != A.slot) continue;
@@ -660,11 +691,18 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             if (A.gview[g] == A.view && (A.gage[g] == 0 || fresh)) srcp[g] = (const uint32_t *)W->lo;
             else srcp[g] = (const uint32_t *)(S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES + band_off);
         }
-#pragma unroll 3
-        for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {
-            uint32_t src[4][3];
 #pragma unroll
-            for (int g = 0; g < 4; g++) { src[g][0] = srcp[g][q * 3]; src[g][1] = srcp[g][q * 3 + 1]; src[g][2] = srcp[g][q * 3 + 2]; }
+        for (int it = 0; it < PRE_IT; it++) {
+            const int q = lane + 32 * it;
+            uint32_t src[4][3];
+            if (use_pre) {
+#pragma unroll
+                for (int g = 0; g < 3; g++) { src[g][0] = pre[it][g][0]; src[g][1] = pre[it][g][1]; src[g][2] = pre[it][g][2]; }
+                src[3][0] = srcp[3][q * 3]; src[3][1] = srcp[3][q * 3 + 1]; src[3][2] = srcp[3][q * 3 + 2];
+            } else {
+#pragma unroll
+                for (int g = 0; g < 4; g++) { src[g][0] = srcp[g][q * 3]; src[g][1] = srcp[g][q * 3 + 1]; src[g][2] = srcp[g][q * 3 + 2]; }
+            }
             uint4 *dst = (uint4 *)(obs_w + (size_t)q * 12);
 #pragma unroll
             for (int half = 0; half < 3; half++) {
