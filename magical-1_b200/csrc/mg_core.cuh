@@ -43,7 +43,10 @@ MG_HD vec2 vperp(vec2 a) { return V(-a.y, a.x); }
 MG_HD vec2 vrot(vec2 a, vec2 b) { return V(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 MG_HD vec2 vlerp(vec2 a, vec2 b, double t) { return vadd(vmul(a, 1.0 - t), vmul(b, t)); }
 MG_HD double clamp01(double f) { return f < 0.0 ? 0.0 : (f > 1.0 ? 1.0 : f); }
-MG_HD double dclamp(double f, double lo, double hi) { return fmin(fmax(f, lo), hi); }
+/* chipmunk.h: cpfmax(a, b) = (a > b) ? a : b, cpfmin(a, b) = (a < b) ? a : b, cpfclamp = cpfmin(cpfmax(f, lo), hi) */
+MG_HD double cp_max(double a, double b) { return a > b ? a : b; }
+MG_HD double cp_min(double a, double b) { return a < b ? a : b; }
+MG_HD double dclamp(double f, double lo, double hi) { return cp_min(cp_max(f, lo), hi); }
 
 /* ------------------------------------------------------------------ geometry tables */
 

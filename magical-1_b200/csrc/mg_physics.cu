@@ -544,7 +544,7 @@ __device__ void arb_prestep(EnvRef e, int s, double slop, double bias_c)
         ACF(e, s, k, AC_NMASS) = 1.0 / k_scalar(e, a, b, r1, r2, n);
         ACF(e, s, k, AC_TMASS) = 1.0 / k_scalar(e, a, b, r1, r2, vperp(n));
         double dist = vdot(vadd(vsub(r2, r1), body_delta), n);
-        ACF(e, s, k, AC_BIAS) = -bias_c * fmin(0.0, dist + slop) / dt;
+        ACF(e, s, k, AC_BIAS) = -bias_c * cp_min(0.0, dist + slop) / dt;
         ACF(e, s, k, AC_JBIAS) = 0.0;
         /* bounce = normal_relative_velocity * e with e = 0 for every shape */
     }
@@ -583,11 +583,11 @@ __device__ void arb_apply_impulse(EnvRef e, int s)
         double vrt = vdot(vr, vperp(n));
         double jbn = (ACF(e, s, k, AC_BIAS) - vbn) * n_mass;
         double jbn_old = ACF(e, s, k, AC_JBIAS);
-        double j_bias = fmax(jbn_old + jbn, 0.0);
+        double j_bias = cp_max(jbn_old + jbn, 0.0);
         ACF(e, s, k, AC_JBIAS) = j_bias;
         double jn = -(0.0 + vrn) * n_mass;
         double jn_old = ACF(e, s, k, AC_JN);
-        double jn_acc = fmax(jn_old + jn, 0.0);
+        double jn_acc = cp_max(jn_old + jn, 0.0);
         ACF(e, s, k, AC_JN) = jn_acc;
         double jt_max = friction * jn_acc;
         double jt = -vrt * ACF(e, s, k, AC_TMASS);

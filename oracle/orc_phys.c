@@ -24,7 +24,10 @@ static inline double vcross(vec a, vec b) { return a.x * b.y - a.y * b.x; }
 static inline vec vneg(vec a) { vec r = { -a.x, -a.y }; return r; }
 static inline vec vperp(vec a) { vec r = { -a.y, a.x }; return r; }
 static inline vec vrotate(vec a, vec b) { vec r = { a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x }; return r; }
-static inline double fclamp(double f, double lo, double hi) { return fmin(fmax(f, lo), hi); }
+/* chipmunk.h: cpfmax(a, b) = (a > b) ? a : b, cpfmin(a, b) = (a < b) ? a : b, cpfclamp = cpfmin(cpfmax(f, lo), hi) */
+static inline double cp_max(double a, double b) { return a > b ? a : b; }
+static inline double cp_min(double a, double b) { return a < b ? a : b; }
+static inline double fclamp(double f, double lo, double hi) { return cp_min(cp_max(f, lo), hi); }
 static inline vec vclamp(vec v, double len)
 {
     /* cpvclamp: (dot > len^2) ? normalize(v) * len : v */
@@ -292,7 +295,7 @@ static void arb_prestep(orc_env *e, orc_arbiter *arb, double dt, double slop, do
         con->n_mass = 1.0 / k_scalar(a, b, con->r1, con->r2, n);
         con->t_mass = 1.0 / k_scalar(a, b, con->r1, con->r2, vperp(n));
         double dist = vdot(vadd(vsub(con->r2, con->r1), body_delta), n);
-        con->bias = -bias * fmin(0.0, dist + slop) / dt;
+        con->bias = -bias * cp_min(0.0, dist + slop) / dt;
         con->j_bias = 0.0;
         con->bounce = vdot(relative_velocity(a, b, con->r1, con->r2), n) * arb->e;
     }
@@ -329,10 +332,10 @@ static void arb_apply_impulse(orc_env *e, orc_arbiter *arb)
         double vrt = vdot(vr, vperp(n));
         double jbn = (con->bias - vbn) * n_mass;
         double jbn_old = con->j_bias;
-        con->j_bias = fmax(jbn_old + jbn, 0.0);
+        con->j_bias = cp_max(jbn_old + jbn, 0.0);
         double jn = -(con->bounce + vrn) * n_mass;
         double jn_old = con->jn_acc;
-        con->jn_acc = fmax(jn_old + jn, 0.0);
+        con->jn_acc = cp_max(jn_old + jn, 0.0);
         double jt_max = friction * con->jn_acc;
         double jt = -vrt * con->t_mass;
         double jt_old = con->jt_acc;
