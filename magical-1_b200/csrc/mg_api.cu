@@ -13,6 +13,8 @@
 #include "mg_tables.h"
 #include "../../include/mg_trig.h"
 
+#define MG_HOST_CHUNKS 8   /* parts of the batch whose D2H copy overlaps the rendering of the next (mg_step_host) */
+
 struct mg_handle {
     mg_config cfg;
     MgDeviceState S;
@@ -29,7 +31,8 @@ struct mg_handle {
     float *reward_dev, *score_dev;
     uint8_t *done_dev;
     size_t obs_bytes;
-    cudaStream_t own_stream;
+    cudaStream_t own_stream, copy_stream;   /* mg_step_host: compute stream and the stream of the chunked D2H copies */
+    cudaEvent_t chunk_done[MG_HOST_CHUNKS];
     /* accounting */
     int64_t launches;
     int timing;
@@ -117,6 +120,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaMalloc(&h->score_dev, (size_t)B * sizeof(float)));
     CK(h, cudaMalloc(&h->done_dev, (size_t)B));
     CK(h, cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
+    CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int c = 0; c < MG_HOST_CHUNKS; c++) CK(h, cudaEventCreateWithFlags(&h->chunk_done[c], cudaEventDisableTiming));
     *out = h;
     return MG_OK;
 }
@@ -131,7 +136,8 @@ extern "C" int mg_destroy(mg_handle *h)
     for (int v = 0; v < 2; v++) { cudaFree(h->S.sprims[v]); cudaFree(h->S.sverts[v]); cudaFree(h->S.dashv[v]); }
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
-    cudaStreamDestroy(h->own_stream);
+    cudaStreamDestroy(h->own_stream); cudaStreamDestroy(h->copy_stream);
+    for (int c = 0; c < MG_HOST_CHUNKS; c++) cudaEventDestroy(h->chunk_done[c]);
     for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (auto e : h->free_events) cudaEventDestroy(e);
     delete h;
@@ -217,7 +223,7 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
     for (int v = 0; v < 2; v++) {
         if (!h->spec.render_view[v]) continue;
         bool fuse = h->fused && v == last_view && obs_dev;
-        mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, st);
+        mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, 0, h->cfg.num_envs, st);
         nl++;
     }
     time_end(h, 1, nl, st);      /* one timed unit = geometry + raster launch of one view */
@@ -246,13 +252,39 @@ extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *
     cudaStream_t st = h->own_stream;
     CK(h, cudaSetDevice(h->cfg.device));
     CK(h, cudaMemcpyAsync(h->actions_dev, actions_host, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-    int rc = mg_step(h, h->actions_dev, h->obs_dev, h->reward_dev, h->done_dev, h->score_dev, st);
+    int rc = mg_step_physics(h, h->actions_dev, h->reward_dev, h->done_dev, h->score_dev, st);
     if (rc != MG_OK) return rc;
-    if (obs_host && h->spec.n_groups > 0) CK(h, cudaMemcpyAsync(obs_host, h->obs_dev, h->obs_bytes, cudaMemcpyDeviceToHost, st));
+    const bool want_obs = obs_host && h->spec.n_groups > 0;
+    if (h->fused && want_obs && B >= 4 * MG_HOST_CHUNKS) {
+        /* single-view HWC stack: render the batch in MG_HOST_CHUNKS parts and start the device-to-host copy of
+         * each part as soon as it is rendered, so the PCIe transfer (the long pole: 110 KB per env) overlaps
+         * the rendering of the following parts */
+        int view = -1;
+        for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) view = v;
+        h->slots[view] = (h->slots[view] + 1) & (MG_MAX_RING - 1);
+        const size_t env_bytes = h->obs_bytes / (size_t)B;
+        for (int c = 0; c < MG_HOST_CHUNKS; c++) {
+            const int e0 = (int)((long long)B * c / MG_HOST_CHUNKS), e1 = (int)((long long)B * (c + 1) / MG_HOST_CHUNKS);
+            mg_launch_render_push(h->S, view, h->slots[view], &h->spec, h->slots, h->obs_dev, e0, e1, st);
+            CK(h, cudaEventRecord(h->chunk_done[c], st));
+            CK(h, cudaStreamWaitEvent(h->copy_stream, h->chunk_done[c], 0));
+            CK(h, cudaMemcpyAsync(obs_host + (size_t)e0 * env_bytes, h->obs_dev + (size_t)e0 * env_bytes,
+                                  (size_t)(e1 - e0) * env_bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+        }
+        mg_launch_clear_fresh(h->S, st);
+        h->launches += 2 * MG_HOST_CHUNKS + 1;
+        rc = check_launch(h, "mg_render_kernel");
+        if (rc != MG_OK) return rc;
+    } else {
+        rc = mg_step_render(h, h->obs_dev, st);
+        if (rc != MG_OK) return rc;
+        if (want_obs) CK(h, cudaMemcpyAsync(obs_host, h->obs_dev, h->obs_bytes, cudaMemcpyDeviceToHost, st));
+    }
     if (reward_host) CK(h, cudaMemcpyAsync(reward_host, h->reward_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (done_host) CK(h, cudaMemcpyAsync(done_host, h->done_dev, (size_t)B, cudaMemcpyDeviceToHost, st));
     if (score_host) CK(h, cudaMemcpyAsync(score_host, h->score_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
     CK(h, cudaStreamSynchronize(st));
+    CK(h, cudaStreamSynchronize(h->copy_stream));
     return MG_OK;
 }
 

@@ -41,12 +41,13 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st);
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);
 /* render `view` of every env and push the 96x96 frame into ring slot `slot`; when `fused` is given the
- * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v) */
+ * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v); envs
+ * [env_begin, env_end) only, so that a host copy of one part can overlap the rendering of the next */
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
-                           uint8_t *obs, cudaStream_t st);
+                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st);
 /* transform every primitive of every env into the screen space of `view` (must precede the render launches
  * of that view whenever poses or scenes changed) */
-void mg_launch_geometry(const MgDeviceState &S, int view, cudaStream_t st);
+void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st);
 /* compose the stacked observation from the rings (any view mix, HWC or CHW) */
 void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int *slots, uint8_t *obs, cudaStream_t st);
 /* clear the per-env "fresh" flag after all views were pushed */

@@ -390,6 +390,7 @@ struct RenderArgs {
     uint8_t *obs;
     int n_groups;
     int gview[MG_MAX_GROUPS], gslot[MG_MAX_GROUPS], gage[MG_MAX_GROUPS];
+    int env_begin, env_end;   /* envs [env_begin, env_end) of the batch */
 };
 
 /* ---------------------------------------------------------------- geometry pass
@@ -397,12 +398,12 @@ struct RenderArgs {
  * (Viewer.render -> Geom.render -> stack.apply_current_matrix, render.py:116-160, 373-392), transforms the
  * vertices in FP64 and truncates them the way pygame converts its float arguments to int.  The band
  * rasterisers then only see integers. */
-__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view)
+__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view, int env_begin, int env_end)
 {
     const MgTables *T = S.tables;
     const int lane = threadIdx.x & 31;
-    const int env = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (env >= S.num_envs) return;
+    const int env = env_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (env >= env_end) return;
     const double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
     const double *rp = pose + MG_BODY_ROBOT * MG_POSE_NF;
     const aff cam = view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
@@ -498,8 +499,8 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     __syncthreads();
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
-    int env = (int)(item / N_BANDS), band = (int)(item % N_BANDS);
-    if (env >= S.num_envs) return;
+    int env = A.env_begin + (int)(item / N_BANDS), band = (int)(item % N_BANDS);
+    if (env >= A.env_end) return;
     WarpSmem *W = (WarpSmem *)smem_raw + warp;
     const int y0 = band * BAND_ROWS;
 
@@ -763,14 +764,16 @@ __global__ void mg_clear_fresh_kernel(MgDeviceState S)
     if (env < S.num_envs) S.istate[mg_field_index(env, I_NF, I_FRESH)] = 0;
 }
 
-void mg_launch_geometry(const MgDeviceState &S, int view, cudaStream_t st)
+void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st)
 {
-    mg_geometry_kernel<<<(S.num_envs + 3) / 4, 128, 0, st>>>(S, view);
+    if (env_end <= env_begin) return;
+    mg_geometry_kernel<<<(env_end - env_begin + 3) / 4, 128, 0, st>>>(S, view, env_begin, env_end);
 }
 
 static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st)
 {
-    mg_launch_geometry(S, A.view, st);
+    if (A.env_end <= A.env_begin) return;
+    mg_launch_geometry(S, A.view, A.env_begin, A.env_end, st);
     static bool attr_set = false;
     size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA;
     if (!attr_set) {
@@ -781,7 +784,7 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
         cudaFuncSetAttribute(mg_render_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = true;
     }
-    long long items = (long long)S.num_envs * N_BANDS;
+    long long items = (long long)(A.env_end - A.env_begin) * N_BANDS;
     int grid = (int)((items + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     int variant = A.mode == 0 ? (!A.obs ? 0 : (A.n_groups == 4 ? 1 : 2)) : A.mode + 2;
     switch (variant) {
@@ -794,11 +797,11 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
 }
 
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
-                           uint8_t *obs, cudaStream_t st)
+                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st)
 {
     RenderArgs A;
     memset(&A, 0, sizeof(A));
-    A.view = view; A.mode = 0; A.slot = slot;
+    A.view = view; A.mode = 0; A.slot = slot; A.env_begin = env_begin; A.env_end = env_end;
     if (fused && obs) {
         A.obs = obs; A.n_groups = fused->n_groups;
         for (int g = 0; g < fused->n_groups; g++) {
@@ -813,7 +816,7 @@ void mg_launch_render_out(const MgDeviceState &S, int view, int full_res, uint8_
 {
     RenderArgs A;
     memset(&A, 0, sizeof(A));
-    A.view = view; A.mode = full_res ? 2 : 1; A.out = out;
+    A.view = view; A.mode = full_res ? 2 : 1; A.out = out; A.env_begin = 0; A.env_end = S.num_envs;
     launch_render(S, A, st);
 }
 

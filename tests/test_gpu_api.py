@@ -353,3 +353,32 @@ def test_large_batches_tile_consistently(orc, env_id, n_envs, n_unique):
         assert np.abs(got[i, :o.n_bodies, :3] - o.bodies()[:, :3]).max() <= 1e-3, i
         assert _close(host[i][..., 9:], orc.downsample4(o.render(_E))), i
     env.close()
+
+
+@pytest.mark.parametrize('preproc,n_envs', [('LoRes4E', 100), ('LoRes4E', 8), ('LoRes3EA', 40)])
+def test_step_host_matches_device_step(preproc, n_envs):
+    """mg_step_host (host buffers, copies inside the call, D2H of the fused stack overlapped with the rendering
+    in chunks) returns exactly what mg_step leaves on the device."""
+    import torch
+    import magical_b200 as m
+    a = m.make(f'MakeLine-Demo-{preproc}-v0', num_envs=n_envs, seed=31, obs_keys=('past_obs',))
+    b = m.make(f'MakeLine-Demo-{preproc}-v0', num_envs=n_envs, seed=31, obs_keys=('past_obs',))
+    a.auto_reset = b.auto_reset = False
+    a.reset()
+    b.reset([a.scenes[i] for i in range(n_envs)])
+    obs_h = torch.empty((n_envs, 96, 96, 12), dtype=torch.uint8).pin_memory()
+    rew_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
+    done_h = torch.empty(n_envs, dtype=torch.uint8).pin_memory()
+    score_h = torch.empty(n_envs, dtype=torch.float32).pin_memory()
+    act_h = torch.empty(n_envs, dtype=torch.int32).pin_memory()
+    rs = np.random.RandomState(4)
+    for t in range(6):
+        acts = rs.randint(0, 18, size=n_envs)
+        act_h.copy_(torch.from_numpy(acts.astype(np.int32)))
+        obs_h.fill_(0)
+        a.step_host(act_h, obs_h, rew_h, done_h, score_h)
+        obs, rew, done, info = b.step(acts)
+        np.testing.assert_array_equal(obs_h.numpy(), obs['past_obs'].cpu().numpy())
+        np.testing.assert_array_equal(rew_h.numpy(), rew.cpu().numpy())
+        np.testing.assert_array_equal(done_h.numpy().astype(bool), done.cpu().numpy())
+    a.close(); b.close()
