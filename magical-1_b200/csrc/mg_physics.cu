@@ -1,7 +1,7 @@
 /*
  * mg_physics.cu -- reset expansion, the per-step rigid-body kernel and the score kernels.
  *
- * One thread owns one env (one pymunk Space of the reference) and runs, in Chipmunk's
+ * One group of PHYS_LANES lanes owns one env (one pymunk Space of the reference) and runs, in Chipmunk's
  * order, everything BaseEnv.step does before rendering (magical/base_env.py:267-292):
  *   Robot.set_action                      magical/entities.py:435-453
  *   10 x ( Robot.update ; Space.step )    magical/base_env.py:248-255, magical/entities.py:455-476
@@ -12,8 +12,11 @@
  * pre-step, cached impulses, 10 sequential-impulse iterations over arbiters then
  * constraints in add order.  All arithmetic is IEEE double without FMA contraction.
  *
- * Lanes of a warp are 32 different envs; state is field-major per 32-env group
- * (mg_state.cuh), so every state access of a warp is one 256-byte row.
+ * The env's bodies, constraints and shape list are staged in shared memory for the whole step; items that
+ * do not depend on each other (bodies, shape pairs, pre-steps) are spread over the group's lanes, and the
+ * order-dependent half of every sub-step runs on one lane per env, the lanes of all envs of a CTA side by
+ * side in warp 0 (space_step_parallel / space_step_serial).  Every scalar goes through the same operations
+ * in the same order as in a serial cpSpaceStep, so the result does not depend on the mapping.
  */
 #include <cuda_runtime.h>
 #include <stdlib.h>
