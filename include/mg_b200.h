@@ -25,6 +25,8 @@
  *   mg_host_entity_overlaps   space.shape_query in the placement     magical/geom.py:226-233
  *                             sampler (host-side reset only)
  *   mg_host_palette           style.COLOURS_RGB / darken / lighten   magical/style.py:10-37
+ *   mg_host_sample_scene(s)   BaseEnv.reset() up to the first render magical/base_env.py:190-246, geom.py:116-384,
+ *                             (phys vars, on_reset of the 9 tasks)   benchmarks/*.py on_reset; rng = RandomState stream
  *
  * Conventions: plain pointers and sizes; no exceptions cross the boundary; every call
  * returns 0 on success or a negative MG_ERR_* code and records a message readable with
@@ -49,6 +51,7 @@ extern "C" {
 #define MG_ERR_ARG (-1)
 #define MG_ERR_CUDA (-2)
 #define MG_ERR_NODEVICE (-3)
+#define MG_ERR_PLACEMENT (-4)   /* geom.PlacementError: an entity could not be placed (geom.py:111-113, 256-259) */
 
 #define MG_VIEW_ALLO 0
 #define MG_VIEW_EGO 1
@@ -141,6 +144,32 @@ int mg_host_entity_overlaps(const mg_scene *scene, int kind, int idx, int robot_
  * twice-lightened colour for red, green, blue, yellow (magical/style.py:10-37, render.py:146-149).
  * Returns the number of entries written to rgb_out[n][3]. */
 int mg_host_palette(uint8_t *rgb_out);
+
+/* ---- native host reset engine (CPU only; no device needed) ----
+ * What BaseEnv.reset() does before the first render, for one env: phys-var sampling, the task's on_reset
+ * and the rejection sampler of geom.pm_randomise_all_poses, consuming the env's numpy-legacy MT19937 stream
+ * (np.random.RandomState) draw for draw like the reference consumes self.rng.  The caller owns the stream:
+ * mt_key[624] / *mt_pos are RandomState.get_state()[1:3] and are advanced in place (set_state them back).
+ * kw[] are the task's boolean keyword arguments in this order:
+ *   MoveToCorner, PickAndPlace : rand_shape_colour, rand_shape_type, rand_poses, debug_reward
+ *   MoveToRegion               : rand_poses_minor, rand_poses_full, rand_goal_colour
+ *   MatchRegions               : rand_target_colour, rand_shape_type, rand_shape_count, rand_layout_minor, rand_layout_full
+ *   MakeLine, FindDupe, FixColour : rand_colours, rand_shapes, rand_count, rand_layout_minor, rand_layout_full
+ *   ClusterColour, ClusterShape   : rand_shape_colour, rand_shape_type, rand_layout_minor, rand_layout_full, rand_shape_count
+ * Returns MG_OK, MG_ERR_ARG, or MG_ERR_PLACEMENT where the reference raises PlacementError (the stream has
+ * then advanced exactly as far as the reference's would have). */
+typedef struct mg_reset_spec {
+    int32_t task;            /* MG_TASK_* */
+    int32_t horizon;         /* max_episode_steps */
+    int32_t rand_dynamics;
+    int32_t kw[8];
+    int32_t reserved;
+} mg_reset_spec;
+
+int mg_host_sample_scene(const mg_reset_spec *spec, uint32_t *mt_key, int32_t *mt_pos, mg_scene *out);
+/* n envs at once on n_threads host threads: specs[n], mt_keys[n][624], mt_pos[n], out[n], status[n] */
+int mg_host_sample_scenes(const mg_reset_spec *specs, int n, uint32_t *mt_keys, int32_t *mt_pos, mg_scene *out,
+                          int32_t *status, int n_threads);
 
 #ifdef __cplusplus
 }

@@ -57,6 +57,14 @@ class Config(C.Structure):
                 ('chw', C.c_int32), ('reserved', C.c_int32 * 5)]
 
 
+class ResetSpec(C.Structure):
+    """mg_reset_spec: task, horizon, rand_dynamics and the task's boolean kwargs in header order."""
+    _fields_ = [('task', C.c_int32), ('horizon', C.c_int32), ('rand_dynamics', C.c_int32),
+                ('kw', C.c_int32 * 8), ('reserved', C.c_int32)]
+
+
+ERR_PLACEMENT = -4
+
 # every symbol include/mg_b200.h declares: name -> (restype, argtypes)
 _VP = C.c_void_p
 SYMBOLS = {
@@ -81,6 +89,8 @@ SYMBOLS = {
     'mg_kernel_ms': (C.c_double, [_VP, C.c_int, C.c_int, C.POINTER(C.c_int64)]),
     'mg_host_palette': (C.c_int, [_VP]),
     'mg_host_entity_overlaps': (C.c_int, [C.POINTER(Scene), C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32]),
+    'mg_host_sample_scene': (C.c_int, [C.POINTER(ResetSpec), _VP, _VP, C.POINTER(Scene)]),
+    'mg_host_sample_scenes': (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, C.c_int]),
 }
 
 _lib = None

@@ -8,6 +8,7 @@ module samples resets on the host (tasks.py), owns the torch tensors that receiv
 and keeps the per-env episode counters.  torch is used for device memory and streams only.
 """
 import collections
+import os
 import ctypes as C
 
 import numpy as np
@@ -65,6 +66,9 @@ class BatchedMagicalEnv:
             self._specs = list(env_ids)
             assert len(self._specs) == self.num_envs
         self._horizons = np.asarray([s[2] for s in self._specs], np.int64)
+        self._reset_spec_cache = {}
+        self._py_reset = os.environ.get('MG_PY_RESET', '0') == '1'
+        self._reset_threads = max(1, len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1))
         spec = PREPROC_SPECS[preproc] if preproc is not None else dict(groups=[], kind='none', chw=False)
         self._pspec = spec
         groups = spec['groups']
@@ -132,16 +136,76 @@ class BatchedMagicalEnv:
         if seed is None:
             seed = np.random.randint(0, (1 << 31) - 1)
         self._seed = int(seed)
-        self.rngs = [np.random.RandomState((self._seed + i) % (1 << 32)) for i in range(self.num_envs)]
+        # the streams live as raw MT19937 states (RandomState.get_state()[1:3]) so that the native reset engine
+        # can advance thousands of them without a Python object per env; `rngs` rebuilds RandomStates on demand
+        B = self.num_envs
+        self._mt_keys = np.empty((B, 624), np.uint32)
+        self._mt_pos = np.empty(B, np.int32)
+        for i in range(B):
+            st = np.random.RandomState((self._seed + i) % (1 << 32)).get_state()
+            self._mt_keys[i], self._mt_pos[i] = st[1], st[2]
         return [self._seed]
 
-    def _sample(self, i):
+    @property
+    def rngs(self):
+        """np.random.RandomState per env, positioned where the env's stream currently is (copies)."""
+        out = []
+        for i in range(self.num_envs):
+            r = np.random.RandomState(0)
+            r.set_state(('MT19937', self._mt_keys[i], int(self._mt_pos[i]), 0, 0.0))
+            out.append(r)
+        return out
+
+    def _task_kwargs(self, i):
         ep, kw, horizon = self._specs[i]
         kw = dict(kw)
         rand_dynamics = kw.pop('rand_dynamics', False)
         for k in ('res_hw', 'fps', 'phys_steps', 'phys_iter', 'max_episode_steps'):
             kw.pop(k, None)
-        return tasks.sample_scene(ep, self.rngs[i], horizon, rand_dynamics=rand_dynamics, **kw)
+        return ep, horizon, rand_dynamics, kw
+
+    def _reset_spec(self, i):
+        key = id(self._specs[i])
+        if key not in self._reset_spec_cache:
+            ep, horizon, rand_dynamics, kw = self._task_kwargs(i)
+            self._reset_spec_cache[key] = tasks.reset_spec(ep, horizon, rand_dynamics, **kw)
+        return self._reset_spec_cache[key]
+
+    def _sample(self, i):
+        """One env through the Python specification (tasks.py), on the env's own stream."""
+        ep, horizon, rand_dynamics, kw = self._task_kwargs(i)
+        r = np.random.RandomState(0)
+        r.set_state(('MT19937', self._mt_keys[i], int(self._mt_pos[i]), 0, 0.0))
+        try:
+            return tasks.sample_scene(ep, r, horizon, rand_dynamics=rand_dynamics, **kw)
+        finally:
+            st = r.get_state()
+            self._mt_keys[i], self._mt_pos[i] = st[1], st[2]
+
+    def _sample_many(self, env_ids):
+        """BaseEnv.reset()'s sampling for the given envs: the native engine (csrc/mg_reset.cpp) on all host
+        cores, each env on its own RandomState stream; MG_PY_RESET=1 runs the Python specification instead.
+        Unlike a sequential loop, a PlacementError is raised after every env's stream has advanced."""
+        env_ids = np.asarray(env_ids, np.int64)
+        if self._py_reset:
+            return [self._sample(int(i)) for i in env_ids]
+        n = len(env_ids)
+        specs = (L.ResetSpec * n)(*[self._reset_spec(int(i)) for i in env_ids])
+        keys = np.ascontiguousarray(self._mt_keys[env_ids])
+        pos = np.ascontiguousarray(self._mt_pos[env_ids])
+        scenes = (L.Scene * n)()
+        status = np.zeros(n, np.int32)
+        rc = self._lib.mg_host_sample_scenes(C.addressof(specs), n, keys.ctypes.data, pos.ctypes.data,
+                                             C.addressof(scenes), status.ctypes.data, self._reset_threads)
+        if rc != 0:
+            raise L.MgError(f'mg_host_sample_scenes failed ({rc})')
+        self._mt_keys[env_ids], self._mt_pos[env_ids] = keys, pos
+        bad = np.nonzero(status)[0]
+        if len(bad):
+            if (status[bad] == L.ERR_PLACEMENT).all():
+                raise tasks.PlacementError(f'Could not place an entity in env(s) {env_ids[bad].tolist()[:8]}')
+            raise L.MgError(f'native reset failed for envs {env_ids[bad].tolist()[:8]}: {status[bad].tolist()[:8]}')
+        return [scenes[k] for k in range(n)]
 
     def set_scenes(self, env_ids, scenes):
         """Install explicit initial states (used by reset and by the parity tests)."""
@@ -160,7 +224,7 @@ class BatchedMagicalEnv:
 
     def reset(self, scenes=None):
         if scenes is None:
-            scenes = [self._sample(i) for i in range(self.num_envs)]
+            scenes = self._sample_many(np.arange(self.num_envs))
         self.set_scenes(np.arange(self.num_envs), scenes)
         self._check(self._lib.mg_reset_obs(self._h, L.ptr(self._obs), self._stream()))
         self._needs_reset = False
@@ -186,7 +250,7 @@ class BatchedMagicalEnv:
         if len(finished) and self.auto_reset:
             # results of the finished episodes must survive the next step's writes
             reward, score = reward.clone(), score.clone()
-            self.set_scenes(finished, [self._sample(int(i)) for i in finished])
+            self.set_scenes(finished, self._sample_many(finished))
         self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
         return self._make_obs(), reward, done, {'eval_score': score}
 

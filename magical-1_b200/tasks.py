@@ -589,3 +589,99 @@ def sample_scene(entry_point, rng, max_episode_steps, rand_dynamics=False, **tas
     b = SceneBuilder(task, max_episode_steps, rng, rand_dynamics)
     fn(b, **fixed, **task_kwargs)
     return b.scene
+
+
+# --------------------------------------------------------------------------- native engine (csrc/mg_reset.cpp)
+
+# order of each task's boolean kwargs in mg_reset_spec.kw (include/mg_b200.h)
+_KW_ORDER = {
+    L.TASK_MOVE_TO_CORNER: ('rand_shape_colour', 'rand_shape_type', 'rand_poses', 'debug_reward'),
+    L.TASK_PICK_AND_PLACE: ('rand_shape_colour', 'rand_shape_type', 'rand_poses', 'debug_reward'),
+    L.TASK_MOVE_TO_REGION: ('rand_poses_minor', 'rand_poses_full', 'rand_goal_colour'),
+    L.TASK_MATCH_REGIONS: ('rand_target_colour', 'rand_shape_type', 'rand_shape_count', 'rand_layout_minor',
+                           'rand_layout_full'),
+    L.TASK_MAKE_LINE: ('rand_colours', 'rand_shapes', 'rand_count', 'rand_layout_minor', 'rand_layout_full'),
+    L.TASK_FIND_DUPE: ('rand_colours', 'rand_shapes', 'rand_count', 'rand_layout_minor', 'rand_layout_full'),
+    L.TASK_FIX_COLOUR: ('rand_colours', 'rand_shapes', 'rand_count', 'rand_layout_minor', 'rand_layout_full'),
+    L.TASK_CLUSTER_COLOUR: ('rand_shape_colour', 'rand_shape_type', 'rand_layout_minor', 'rand_layout_full',
+                            'rand_shape_count'),
+    L.TASK_CLUSTER_SHAPE: ('rand_shape_colour', 'rand_shape_type', 'rand_layout_minor', 'rand_layout_full',
+                           'rand_shape_count'),
+}
+
+
+def _check_flag_combinations(task, kw):
+    """The assertions the reference's on_resets make on their flags (e.g. cluster.py:56-65)."""
+    if task in (L.TASK_MAKE_LINE, L.TASK_FIND_DUPE, L.TASK_FIX_COLOUR) and kw.get('rand_count'):
+        assert kw.get('rand_layout_full') and kw.get('rand_shapes') and kw.get('rand_colours')
+    if task == L.TASK_MATCH_REGIONS and kw.get('rand_shape_count'):
+        assert kw.get('rand_layout_full') and kw.get('rand_shape_type') and kw.get('rand_target_colour')
+    if task in (L.TASK_CLUSTER_COLOUR, L.TASK_CLUSTER_SHAPE):
+        assert not (kw.get('rand_layout_minor') and kw.get('rand_layout_full'))
+        if kw.get('rand_shape_count'):
+            assert kw.get('rand_layout_full') and kw.get('rand_shape_type') and kw.get('rand_shape_colour')
+    if task == L.TASK_MOVE_TO_REGION:
+        assert not (kw.get('rand_poses_minor') and kw.get('rand_poses_full'))
+
+
+def reset_spec(entry_point, max_episode_steps, rand_dynamics=False, **task_kwargs):
+    """mg_reset_spec for one registered env (entry point + its kwargs)."""
+    task, _, _ = ENTRY_POINTS[entry_point]
+    names = _KW_ORDER[task]
+    unknown = set(task_kwargs) - set(names)
+    if unknown:
+        raise TypeError(f'unexpected keyword arguments for {entry_point}: {sorted(unknown)}')
+    _check_flag_combinations(task, task_kwargs)
+    spec = L.ResetSpec()
+    spec.task, spec.horizon, spec.rand_dynamics = task, int(max_episode_steps), int(bool(rand_dynamics))
+    for k, name in enumerate(names):
+        spec.kw[k] = int(bool(task_kwargs.get(name, False)))
+    return spec
+
+
+def sample_scene_native(entry_point, rng, max_episode_steps, rand_dynamics=False, **task_kwargs):
+    """sample_scene through the C++ engine: same Scene bytes, same RandomState stream afterwards."""
+    spec = reset_spec(entry_point, max_episode_steps, rand_dynamics, **task_kwargs)
+    name, key, pos, has_gauss, cached = rng.get_state()
+    key = np.ascontiguousarray(key, np.uint32).copy()
+    cpos = L.C.c_int32(int(pos))
+    scene = Scene()
+    rc = L.lib().mg_host_sample_scene(L.C.byref(spec), key.ctypes.data, L.C.addressof(cpos), L.C.byref(scene))
+    rng.set_state((name, key, int(cpos.value), has_gauss, cached))
+    if rc == L.ERR_PLACEMENT:
+        raise PlacementError('Could not place an entity (native reset engine)')
+    if rc != 0:
+        raise RuntimeError(f'mg_host_sample_scene failed ({rc})')
+    return scene
+
+
+def sample_scenes_native(specs, rngs, n_threads=None):
+    """Batch form: specs (ResetSpec per env) and RandomStates per env -> list of Scene (PlacementError for any
+    failure, like a sequential loop over the envs would raise).  Runs on n_threads host threads."""
+    import os
+    n = len(specs)
+    if n == 0:
+        return []
+    if n_threads is None:
+        n_threads = min(n, len(os.sched_getaffinity(0)) if hasattr(os, 'sched_getaffinity') else (os.cpu_count() or 1))
+    spec_arr = (L.ResetSpec * n)(*specs)
+    keys = np.empty((n, 624), np.uint32)
+    pos = np.empty(n, np.int32)
+    states = [r.get_state() for r in rngs]
+    for i, st in enumerate(states):
+        keys[i] = st[1]
+        pos[i] = st[2]
+    scenes = (Scene * n)()
+    status = np.zeros(n, np.int32)
+    rc = L.lib().mg_host_sample_scenes(L.C.addressof(spec_arr), n, keys.ctypes.data, pos.ctypes.data,
+                                       L.C.addressof(scenes), status.ctypes.data, int(n_threads))
+    if rc != 0:
+        raise RuntimeError(f'mg_host_sample_scenes failed ({rc})')
+    for i, (r, st) in enumerate(zip(rngs, states)):
+        r.set_state((st[0], keys[i], int(pos[i]), st[3], st[4]))
+    bad = np.nonzero(status)[0]
+    if len(bad):
+        if (status[bad] == L.ERR_PLACEMENT).all():
+            raise PlacementError(f'Could not place an entity in env(s) {bad.tolist()[:8]} (native reset engine)')
+        raise RuntimeError(f'native reset failed for envs {bad.tolist()[:8]}: {status[bad].tolist()[:8]}')
+    return [L.copy_scene(scenes[i]) for i in range(n)]
