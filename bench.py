@@ -7,8 +7,8 @@ Workload (BASELINE.json configs[1]): MoveToCorner-Demo-LoRes4E-v0, 4096 envs per
 actions, envs sharded by index across ranks with no data-path collective (weak scaling); one NCCL
 all-gather of episode scores when episodes end.  One "step" = one env-step of every env of the batch:
 action decode, 10 physics sub-steps, score at the horizon, ego render at 384^2, 4x area downsample, 4-frame
-stack.  Finished episodes are reset inside the timed region from a pool of initial states that was sampled
-on the host before timing (reference RNG, one RandomState per env).
+stack.  Finished episodes are reset inside the timed region from initial states the native reset engine sampled
+on host threads while the previous episode was running (reference RNG, one RandomState stream per env).
 
 --impl reference times the CPU oracle port (oracle/, the restated pymunk+pygame path; the reference itself
 cannot be imported here: pymunk/pygame/gym are not installed) on all host cores.
@@ -182,8 +182,6 @@ def run_gpu(args, rank, world, local_rank):
     K, W = args.steps, args.warmup
     total_steps = 2 * (W + K) + 4
     horizon = m.spec(ENV_ID)['max_episode_steps']
-    n_episodes = total_steps // horizon + 2
-    pool, _ = sample_pool(m, B, n_episodes, seed0=rank * B)
     env = m.make(ENV_ID, num_envs=B, device=local_rank, seed=rank * B, obs_keys=('past_obs',))
     env.auto_reset = False
     ids = np.arange(B, dtype=np.int32)
@@ -197,9 +195,25 @@ def run_gpu(args, rank, world, local_rank):
     obs, rew, done, score = env._obs, env._reward, env._done, env._score
     stream = torch.cuda.current_stream(dev)
 
+    # initial states of the next episode: the native reset engine (every env on its own RandomState stream)
+    # on host threads, started as soon as the previous reset is installed so that it runs under the episode
+    import threading
+    feeder = {'thread': None, 'scenes': None}
+
+    def feed():
+        feeder['scenes'] = env._sample_many(ids, packed=True)
+
+    def start_feed():
+        feeder['thread'] = threading.Thread(target=feed)
+        feeder['thread'].start()
+
     def reset_all():
-        env.set_scenes_packed(ids, pool[state['episode']], B)
+        feeder['thread'].join()
+        env.set_scenes_packed(ids, feeder['scenes'], B)
         state['episode'] += 1
+        start_feed()
+
+    start_feed()
 
     def dev_step():
         """one pass of the hot path, inputs resident in HBM"""
@@ -288,7 +302,7 @@ def run_gpu(args, rank, world, local_rank):
             'ms_per_step': ms_max / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic',
             'config': {'workload': f'{ENV_ID} x {B} envs per GPU (BASELINE.json configs[1]), scripted random actions, '
-                                   f'horizon {horizon}, resets inside the timed region from a pre-sampled pool',
+                                   f'horizon {horizon}, resets inside the timed region (native reset engine on host threads, sampled while the previous episode runs)',
                        'envs_per_gpu': B, 'obs': 'u8[B,96,96,12] past_obs (4 ego frames)',
                        'l2': f'per-step working set (obs {B * OBS_BYTES_PER_ENV / 1e6:.0f} MB + rings + state) exceeds the 126 MB L2',
                        'parallelism': f'env-sharded x{world}, no data-path collective'},

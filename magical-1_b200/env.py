@@ -182,13 +182,14 @@ class BatchedMagicalEnv:
             st = r.get_state()
             self._mt_keys[i], self._mt_pos[i] = st[1], st[2]
 
-    def _sample_many(self, env_ids):
+    def _sample_many(self, env_ids, packed=False):
         """BaseEnv.reset()'s sampling for the given envs: the native engine (csrc/mg_reset.cpp) on all host
         cores, each env on its own RandomState stream; MG_PY_RESET=1 runs the Python specification instead.
         Unlike a sequential loop, a PlacementError is raised after every env's stream has advanced."""
         env_ids = np.asarray(env_ids, np.int64)
         if self._py_reset:
-            return [self._sample(int(i)) for i in env_ids]
+            out = [self._sample(int(i)) for i in env_ids]
+            return L.scenes_array(out) if packed else out
         n = len(env_ids)
         specs = (L.ResetSpec * n)(*[self._reset_spec(int(i)) for i in env_ids])
         keys = np.ascontiguousarray(self._mt_keys[env_ids])
@@ -205,7 +206,7 @@ class BatchedMagicalEnv:
             if (status[bad] == L.ERR_PLACEMENT).all():
                 raise tasks.PlacementError(f'Could not place an entity in env(s) {env_ids[bad].tolist()[:8]}')
             raise L.MgError(f'native reset failed for envs {env_ids[bad].tolist()[:8]}: {status[bad].tolist()[:8]}')
-        return [scenes[k] for k in range(n)]
+        return scenes if packed else [scenes[k] for k in range(n)]
 
     def set_scenes(self, env_ids, scenes):
         """Install explicit initial states (used by reset and by the parity tests)."""
