@@ -22,6 +22,9 @@
  *   mg_debug_reward           debug_shaped_reward()                  move_to_corner.py:86-100, pick_and_place.py:114-124
  *   mg_get_bodies             body.position/.angle/.velocity reads   magical/base_env.py:358-413 (debug_print_entity_spec)
  *   mg_get_state/mg_set_state (no reference equivalent: EzPickle re-constructs, base_env.py:20-46)
+ *   mg_frames_downsample      ResizeDictObservation on stored frames magical/benchmarks/__init__.py:150-190
+ *   mg_frames_stack           FlattenFrameStack / EagerDictFrameStack / ChannelsFirst replayed over a stored
+ *                             trajectory (preprocess_demos_with_wrapper) magical/saved_trajectories.py:87-149
  *   mg_host_entity_overlaps   space.shape_query in the placement     magical/geom.py:226-233
  *                             sampler (host-side reset only)
  *   mg_host_palette           style.COLOURS_RGB / darken / lighten   magical/style.py:10-37
@@ -127,6 +130,18 @@ int64_t mg_launch_count(const mg_handle *h);
  * with reset != 0; which: 0 physics, 1 render.  Only counted while mg_set_timing(h,1). */
 int mg_set_timing(mg_handle *h, int enable);
 double mg_kernel_ms(mg_handle *h, int which, int reset, int64_t *launches_out);
+
+/* ---- the preprocess half of the path on STORED frames (demo trajectories, saved_trajectories.py:87-149) ----
+ * No handle: `device` is the CUDA ordinal; errors are readable with mg_last_error(NULL).
+ * mg_frames_downsample: cv2.resize(INTER_AREA) 384 -> 96 of n_frames frames, u8 [n,384,384,3] -> [n,96,96,3]
+ * (round-half-even of each 4x4 block mean, as the step kernel does).  frames_dev must be 16-byte aligned. */
+int mg_frames_downsample(int device, const uint8_t *frames_dev, int64_t n_frames, uint8_t *out_dev, void *stream);
+/* mg_frames_stack: frame t of the output is the channel concatenation of the 96x96 frames
+ * (group_view[g], max(t - group_age[g], 0)), g = 0..n_groups-1: what a stacking wrapper returns t steps after
+ * a reset that filled its deque with frame 0.  allo_lo_dev / ego_lo_dev: u8 [n_frames,96,96,3] (either may be
+ * NULL if no group names it); out_dev: u8 [n_frames,96,96,3*n_groups], or [n_frames,3*n_groups,96,96] if chw. */
+int mg_frames_stack(int device, const uint8_t *allo_lo_dev, const uint8_t *ego_lo_dev, int64_t n_frames, int n_groups,
+                    const int32_t *group_view, const int32_t *group_age, int chw, uint8_t *out_dev, void *stream);
 
 /* ---- host-side helpers for reset sampling (no GPU involved) ---- */
 

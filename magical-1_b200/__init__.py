@@ -89,7 +89,9 @@ def update_magical_env_name(env_name, *, task=None, variant=None, preproc=None, 
 
 
 def splice_in_preproc_name(base_env_name, preproc_name):
-    """saved_trajectories.py:52-60."""
+    """saved_trajectories.py:52-60 (the sanity check on the preprocessor name included)."""
+    assert preproc_name in PREPROC_SPECS, \
+        f"no preprocessor named '{preproc_name}', options are {', '.join(PREPROC_SPECS)}"
     return update_magical_env_name(base_env_name, preproc=preproc_name)
 
 

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libmagical_b200.so')
+LIB_PATH = os.environ.get('MG_LIB_PATH') or os.path.join(_HERE, 'libmagical_b200.so')   # MG_LIB_PATH: dev builds (tools/time_variants.py)
 
 MAX_BLOCKS = 10
 MAX_GOALS = 3
@@ -87,6 +87,8 @@ SYMBOLS = {
     'mg_launch_count': (C.c_int64, [_VP]),
     'mg_set_timing': (C.c_int, [_VP, C.c_int]),
     'mg_kernel_ms': (C.c_double, [_VP, C.c_int, C.c_int, C.POINTER(C.c_int64)]),
+    'mg_frames_downsample': (C.c_int, [C.c_int, _VP, C.c_int64, _VP, _VP]),
+    'mg_frames_stack': (C.c_int, [C.c_int, _VP, _VP, C.c_int64, C.c_int, _VP, _VP, C.c_int, _VP, _VP]),
     'mg_host_palette': (C.c_int, [_VP]),
     'mg_host_entity_overlaps': (C.c_int, [C.POINTER(Scene), C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint32]),
     'mg_host_sample_scene': (C.c_int, [C.POINTER(ResetSpec), _VP, _VP, C.POINTER(Scene)]),

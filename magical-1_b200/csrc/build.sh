@@ -5,4 +5,4 @@ set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -std=c++17 -Xcompiler -fPIC,-fno-fast-math,-ffp-contract=off"
-$NVCC $FLAGS -shared -o "${OUT:-../libmagical_b200.so}" mg_api.cu mg_physics.cu mg_raster.cu mg_tables.cpp mg_reset.cpp "$@"
+$NVCC $FLAGS -shared -o "${OUT:-../libmagical_b200.so}" mg_api.cu mg_physics.cu mg_raster.cu mg_frames.cu mg_tables.cpp mg_reset.cpp "$@"

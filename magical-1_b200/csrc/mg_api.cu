@@ -58,6 +58,9 @@ static int fail(mg_handle *h, int code, const std::string &msg)
             return fail(h, MG_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+/* handle-less entry points (mg_frames.cu) report through mg_last_error(NULL) */
+int mg_fail_global(int code, const std::string &msg) { return fail(nullptr, code, msg); }
+
 extern "C" const char *mg_last_error(const mg_handle *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
 
 extern "C" int mg_create(const mg_config *cfg, mg_handle **out)

@@ -613,6 +613,9 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 }
 
 
+#ifndef PHYS_DBG_SKIP
+#define PHYS_DBG_SKIP 0    /* timing experiments only: 1 skips the serial half, 2 the parallel half */
+#endif
 #ifndef PHYS_REGSOLVER
 #define PHYS_REGSOLVER 1   /* robot constraints with body velocities in registers */
 #endif
@@ -636,7 +639,7 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 /* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
 struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
 
-__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch)
+__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, double *bbs)
 {
     const int gl = lane & (PHYS_LANES - 1);     /* lane within the env's group */
     const double dt = MG_DT;
@@ -680,12 +683,19 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
      * after the other in j order -- the order a serial double loop discovers them in */
     int n_live = 0;
     const int ns = IF(e, I_NSHAPES);
+    /* cpShapeCacheBB once per shape and sub-step (lane = shape): the pair loop below only compares boxes */
+    MG_NOUNROLL
+    for (int s = gl; s < ns; s += PHYS_LANES) {
+        const int info = IF(e, I_SHAPE0 + s);
+        const int body = (info >> 8) & 255;
+        tpl_world_bb(T, info & 255, body_p(e, body), body_rot(e, body), bbs + 4 * s);
+    }
+    __syncwarp(gmask);
     MG_NOUNROLL
     for (int i = 0; i + 1 < ns; i++) {
         const int info_i = IF(e, I_SHAPE0 + i);
         const int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
-        const vec2 pi = body_p(e, body_i);
-        const double ri = shape_bound(T, tpl_i);
+        const double bi0 = bbs[4 * i], bi1 = bbs[4 * i + 1], bi2 = bbs[4 * i + 2], bi3 = bbs[4 * i + 3];
         bool si_built = false;
         MG_NOUNROLL
         for (int j0 = i + 1; j0 < ns; j0 += PHYS_LANES) {
@@ -694,33 +704,14 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
             bool cand = false;
             if (j < ns) {
                 info_j = IF(e, I_SHAPE0 + j);
-                const int ent_j = info_j >> 16;
                 /* same body, ShapeFilter group (robot: 1, star pieces), static-static */
-                cand = ent_i != ent_j;
-                const int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
-                const vec2 pj = body_p(e, body_j);
-                if (cand) {
-                    double rj = shape_bound(T, tpl_j) + 1e-6;
-                    if (tpl_i >= MG_TPL_WALL0) {
-                        /* wall i (radius 1) against the bounding circle of shape j */
-                        int w = tpl_i - MG_TPL_WALL0;
-                        vec2 wa = T->wall_a[w], wb = T->wall_b[w];
-                        if (fmin(wa.x, wb.x) - 1.0 > pj.x + rj || fmax(wa.x, wb.x) + 1.0 < pj.x - rj ||
-                            fmin(wa.y, wb.y) - 1.0 > pj.y + rj || fmax(wa.y, wb.y) + 1.0 < pj.y - rj) cand = false;
-                    } else {
-                        vec2 d = vsub(pj, pi);
-                        double rr = ri + rj;
-                        if (vdot(d, d) > rr * rr) cand = false;
-                    }
-                }
+                cand = ent_i != (info_j >> 16);
                 if (cand) {
                     /* bounding boxes (Chipmunk's own broadphase criterion): shapes whose boxes are apart by
-                     * more than rounding noise cannot produce a contact; this needs no shape in memory */
-                    double bi[4], bj[4];
-                    tpl_world_bb(T, tpl_i, pi, body_rot(e, body_i), bi);
-                    tpl_world_bb(T, tpl_j, pj, body_rot(e, body_j), bj);
+                     * more than rounding noise cannot produce a contact */
+                    const double *bj = bbs + 4 * j;
                     const double eps = 1e-9;
-                    if (bi[0] > bj[2] + eps || bj[0] > bi[2] + eps || bi[1] > bj[3] + eps || bj[1] > bi[3] + eps) cand = false;
+                    if (bi0 > bj[2] + eps || bj[0] > bi2 + eps || bi1 > bj[3] + eps || bj[1] > bi3 + eps) cand = false;
                 }
             }
             /* narrow phase for the surviving pairs of this row, up to NARROW_SLOTS at a time on their own
@@ -729,7 +720,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
              * would sit in local memory, which has next to no L1 left beside the env state. */
             unsigned todo = __ballot_sync(gmask, cand);
             if (todo) {
-                if (lane == __ffs(todo) - 1 && !si_built) wshape_from_tpl(T, tpl_i, pi, body_rot(e, body_i), &scratch->si);
+                if (lane == __ffs(todo) - 1 && !si_built) wshape_from_tpl(T, tpl_i, body_p(e, body_i), body_rot(e, body_i), &scratch->si);
                 si_built = true;
                 __syncwarp(gmask);
             }
@@ -1237,7 +1228,7 @@ __device__ __noinline__ double env_debug_reward(EnvRef e)
 
 /* the part of one env's state the step touches all the time, in shared memory.  The double block is sized
  * for the largest env of the batch (max_blocks) so that small scenes leave most of the SM's L1 to the tables
- * and the arbiter cache: [ (7 + max_blocks) bodies | (10 + 2 max_blocks) constraints ] */
+ * and the arbiter cache: [ (7 + max_blocks) bodies | (10 + 2 max_blocks) constraints | world boxes of 9 + 6 max_blocks shapes ] */
 struct PhysSmemFixed {
     int i[(I_ARB0 + 3) & ~3];             /* counters, block / goal / constraint / shape infos */
     unsigned char order[MG_NARB + 8];     /* live arbiter slots in discovery order (+ flag bytes) */
@@ -1245,32 +1236,37 @@ struct PhysSmemFixed {
 };
 #define PHYS_TABLE_BYTES ((int)((offsetof(MgTables, dl_off) + 15) & ~15))
 
+/* shapes of the largest env: robot circle, 4 finger quads, 4 walls, and up to MG_STAR_PIECES per block */
+__host__ __device__ inline int phys_max_shapes(int max_blocks) { return 4 + 5 + max_blocks * MG_STAR_PIECES; }
 __host__ __device__ inline int phys_smem_doubles(int max_blocks)
 {
     /* stride = 1 (mod 16) doubles: the solver lanes of neighbouring envs read the same field of their own
      * env at the same time, and this keeps those reads on different shared-memory banks */
-    int n = (1 + MG_RB_COUNT + max_blocks) * B_NF + (10 + 2 * max_blocks) * C_NF;
+    int n = (1 + MG_RB_COUNT + max_blocks) * B_NF + (10 + 2 * max_blocks) * C_NF + 4 * phys_max_shapes(max_blocks);
     return ((n + 15) & ~15) + 1;
 }
 
-__global__ void __launch_bounds__(PHYS_THREADS, 512 / PHYS_THREADS) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
+template <int PHYS_THREADS_T>
+__global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
                                                                 uint8_t *done_out, float *score_out, int max_blocks)
 {
     extern __shared__ __align__(16) unsigned char phys_smem_raw[];
+    constexpr int ENVS = PHYS_THREADS_T / PHYS_LANES;     /* envs per CTA; lanes 0..ENVS-1 of warp 0 run their serial halves */
     const int nd = phys_smem_doubles(max_blocks), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
+    const int bb_off = con_off + (10 + 2 * max_blocks) * C_NF;     /* world boxes of the env's shapes, 4 doubles each */
     /* the collision half of the tables (templates, walls, constants) in shared memory: with the env state
      * resident there is little L1 left, and every table read from HBM/L2 is a ~700-cycle stall on a serial path */
     {
         const double *src = (const double *)S.tables;
         double *dst = (double *)phys_smem_raw;
-        for (int k = threadIdx.x; k < PHYS_TABLE_BYTES / 8; k += PHYS_THREADS) dst[k] = src[k];
+        for (int k = threadIdx.x; k < PHYS_TABLE_BYTES / 8; k += PHYS_THREADS_T) dst[k] = src[k];
     }
-    double *smd = (double *)(phys_smem_raw + PHYS_TABLE_BYTES);                /* [PHYS_ENVS][nd] */
-    PhysSmemFixed *sm = (PhysSmemFixed *)(smd + (size_t)PHYS_ENVS * nd);       /* [PHYS_ENVS] */
+    double *smd = (double *)(phys_smem_raw + PHYS_TABLE_BYTES);                /* [ENVS][nd] */
+    PhysSmemFixed *sm = (PhysSmemFixed *)(smd + (size_t)ENVS * nd);            /* [ENVS] */
     const int lane = threadIdx.x & 31;
     const int grp = threadIdx.x / PHYS_LANES, gl = threadIdx.x % PHYS_LANES;
     const unsigned gmask = (unsigned)((1ull << PHYS_LANES) - 1) << (lane / PHYS_LANES * PHYS_LANES);
-    const int env0 = blockIdx.x * PHYS_ENVS;
+    const int env0 = blockIdx.x * ENVS;
     const int env = env0 + grp;
     const bool active = env < S.num_envs;       /* idle groups of the last CTA still meet the barriers */
     const MgTables *T = (const MgTables *)phys_smem_raw;   /* only the fields before dl_off are valid */
@@ -1293,7 +1289,7 @@ __global__ void __launch_bounds__(PHYS_THREADS, 512 / PHYS_THREADS) mg_physics_k
     e.d = Wd; e.dc = Wd + con_off; e.i = W->i; e.da = g.da; e.ia = g.ia;
 #if PHYS_BARRIER
     /* lane k of warp 0 runs the serial half of the step for env k of this CTA */
-    const bool solver = threadIdx.x < PHYS_ENVS && env0 + lane < S.num_envs;
+    const bool solver = threadIdx.x < ENVS && env0 + lane < S.num_envs;
     EnvRef es = e;
     if (solver) {
         const EnvRef gs = env_ref(S.dstate, S.istate, env0 + lane);
@@ -1331,14 +1327,20 @@ __global__ void __launch_bounds__(PHYS_THREADS, 512 / PHYS_THREADS) mg_physics_k
                 }
             }
             __syncwarp(gmask);
-            int n_live = space_step_parallel(e, T, lane, gmask, W->order, &W->narrow);
+#if PHYS_DBG_SKIP != 2
+            int n_live = space_step_parallel(e, T, lane, gmask, W->order, &W->narrow, Wd + bb_off);
+#else
+            int n_live = 0;
+#endif
             if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
         }
 #if PHYS_BARRIER
         /* the order-dependent halves of all envs of the CTA in neighbouring lanes of warp 0: their serial
-         * chains then cost one instruction stream instead of PHYS_ENVS */
+         * chains then cost one instruction stream instead of ENVS */
         __syncthreads();
+#if PHYS_DBG_SKIP != 1
         if (solver) space_step_serial(es, sm[lane].order, sm[lane].order[MG_NARB + 1]);
+#endif
         __syncthreads();
 #else
         if (active) {
@@ -1421,12 +1423,22 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
     static size_t attr_set = 0;
     if (max_blocks < 0) max_blocks = 0;
     if (max_blocks > MG_MAX_BLOCKS) max_blocks = MG_MAX_BLOCKS;
-    const size_t smem = PHYS_TABLE_BYTES + ((size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed)) * PHYS_ENVS;
-    if (smem > attr_set) {
-        cudaFuncSetAttribute(mg_physics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = smem;
+    /* 16 envs per CTA while two such CTAs fit one SM; larger scenes run 8 envs per CTA so that three (two
+     * at the largest block counts) stay resident instead of one */
+    const size_t per_env = (size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed);
+    const size_t smem_sm = 233472, smem_cta_reserved = 1024;
+    const bool wide = 2 * (PHYS_TABLE_BYTES + per_env * PHYS_ENVS + smem_cta_reserved) <= smem_sm;
+    const int envs = wide ? PHYS_ENVS : PHYS_ENVS / 2;
+    const size_t smem = PHYS_TABLE_BYTES + per_env * envs;
+    const size_t smem_full = PHYS_TABLE_BYTES + per_env * PHYS_ENVS;
+    if (smem_full > attr_set) {
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
+        attr_set = smem_full;
     }
-    mg_physics_kernel<<<(S.num_envs + PHYS_ENVS - 1) / PHYS_ENVS, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks);
+    const int grid = (S.num_envs + envs - 1) / envs;
+    if (wide) mg_physics_kernel<PHYS_THREADS><<<grid, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks);
+    else mg_physics_kernel<PHYS_THREADS / 2><<<grid, PHYS_THREADS / 2, smem, st>>>(S, actions, reward, done, score, max_blocks);
 }
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
 {

@@ -59,6 +59,9 @@ class BatchedMagicalEnv:
         self.preproc = preproc
         self.max_episode_steps = int(max_episode_steps)
         self.auto_reset = auto_reset
+        # resets that raise PlacementError in the reference (geom.py:256-259) raise here too; > 0 re-samples such
+        # envs that many times on their own stream first (what calling reset() again does)
+        self.placement_retries = 0
         # one (entry point, kwargs, horizon) per env allows mixed batches (BASELINE config 5)
         if env_ids is None:
             self._specs = [(entry_point, dict(env_kwargs), self.max_episode_steps)] * self.num_envs
@@ -200,6 +203,17 @@ class BatchedMagicalEnv:
                                              C.addressof(scenes), status.ctypes.data, self._reset_threads)
         if rc != 0:
             raise L.MgError(f'mg_host_sample_scenes failed ({rc})')
+        for _ in range(self.placement_retries):
+            # what a caller of the reference does after a PlacementError: reset() again, the env's stream going on
+            bad = np.nonzero(status == L.ERR_PLACEMENT)[0]
+            if not len(bad):
+                break
+            for k in bad:
+                one = np.zeros(1, np.int32)
+                self._lib.mg_host_sample_scenes(C.addressof(specs) + int(k) * C.sizeof(L.ResetSpec), 1, keys[k:k + 1].ctypes.data,
+                                                pos[k:k + 1].ctypes.data, C.addressof(scenes) + int(k) * C.sizeof(L.Scene),
+                                                one.ctypes.data, 1)
+                status[k] = one[0]
         self._mt_keys[env_ids], self._mt_pos[env_ids] = keys, pos
         bad = np.nonzero(status)[0]
         if len(bad):

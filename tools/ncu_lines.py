@@ -16,10 +16,11 @@ rows = list(csv.reader(out.splitlines()))
 hi = [i for i, r in enumerate(rows) if 'Instructions Executed' in r][0]
 hdr = rows[hi]
 ci, si, ai = hdr.index('Instructions Executed'), hdr.index(os.environ.get('NCU_COL', '# Samples')), hdr.index('Address')
+xi = hdr.index(os.environ['NCU_SUB']) if os.environ.get('NCU_SUB') else None   # NCU_SUB=stall_barrier: samples minus that column
 insts = []
 for r in rows[hi + 1:]:
     try:
-        insts.append((int(r[ci]), int(r[si])))
+        insts.append((int(r[ci]), int(r[si]) - (int(r[xi]) if xi is not None else 0)))
     except (ValueError, IndexError):
         pass
 # nvdisasm: instructions of the function in order, each preceded by "//## File ..., line N" markers
