@@ -614,7 +614,7 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 
 
 #ifndef PHYS_DBG_SKIP
-#define PHYS_DBG_SKIP 0    /* timing experiments only: 1 skips the serial half, 2 the parallel half */
+#define PHYS_DBG_SKIP 0    /* timing experiments only: 1 skips the serial half, 2 the parallel half, 3 the pair loop, 4 boxes + pair loop, 5 constraint pre-steps, 6 position integration */
 #endif
 #ifndef PHYS_REGSOLVER
 #define PHYS_REGSOLVER 1   /* robot constraints with body velocities in registers */
@@ -635,7 +635,177 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
  * pairs, pre-steps) spread over the lanes.  Whatever depends on Chipmunk's order runs on one lane in that
  * order (arbiter cache updates here, the rest in space_step_serial), so the result is the same bit pattern a
  * serial cpSpaceStep produces.  `order` = shared scratch [MG_NARB + 8]; returns the number of live arbiters. */
-#define NARROW_SLOTS 4
+/* ------------------------------------------------------------------ group-cooperative narrow phase
+ * The lanes of an env's group search the faces / feature pairs of ONE shape pair together.  Every candidate
+ * (a face separation, a closest-feature distance) is computed by the same expression as in the serial
+ * collide_* of mg_core.cuh, and the winner is the one the serial loops keep: the first strict maximum /
+ * minimum in loop order (ties go to the lower loop index).  The results are therefore bit-identical. */
+#define GROUP_FOR_XOR for (int off_ = PHYS_LANES / 2; off_ > 0; off_ >>= 1)
+
+/* first maximum: (v, k) over the group, lowest k among equal v */
+__device__ __forceinline__ void group_argmax(unsigned gmask, double &v, int &k)
+{
+    GROUP_FOR_XOR {
+        const double v2 = __shfl_xor_sync(gmask, v, off_);
+        const int k2 = __shfl_xor_sync(gmask, k, off_);
+        if (v2 > v || (v2 == v && k2 < k)) { v = v2; k = k2; }
+    }
+}
+__device__ __forceinline__ void group_argmin(unsigned gmask, double &v, int &k)
+{
+    GROUP_FOR_XOR {
+        const double v2 = __shfl_xor_sync(gmask, v, off_);
+        const int k2 = __shfl_xor_sync(gmask, k, off_);
+        if (v2 < v || (v2 == v && k2 < k)) { v = v2; k = k2; }
+    }
+}
+
+/* wshape_from_tpl with one vertex per lane */
+__device__ void coop_wshape(const MgTables *T, int tpl, vec2 p, vec2 rot, WShape *s, int gl)
+{
+    if (tpl >= MG_TPL_CIRCLE_ROBOT) {
+        if (gl == 0) wshape_from_tpl(T, tpl, p, rot, s);
+        return;
+    }
+    const int n = T->tpl_n[tpl];
+    if (gl == 0) { s->kind = MG_SHAPE_POLY; s->n = n; s->r = T->tpl_r[tpl]; }
+    MG_NOUNROLL
+    for (int i = gl; i < n; i += PHYS_LANES) {
+        vec2 l = T->tpl_v[tpl][i], m = T->tpl_nrm[tpl][i];
+        s->v[i] = V(rot.x * l.x - rot.y * l.y + p.x, rot.y * l.x + rot.x * l.y + p.y);
+        s->nrm[i] = V(rot.x * m.x - rot.y * m.y, rot.y * m.x + rot.x * m.y);
+    }
+}
+
+/* collide_convex_convex (PolyToPoly / SegmentToPoly): lane = face, then lane = (edge, vertex) pair; the lane
+ * that owns the decisive feature pair writes the manifold */
+__device__ void coop_convex_convex(const WShape *A, const WShape *B, Manifold *m, int gl, unsigned gmask)
+{
+    const int An = A->n, Bn = B->n;
+    const double rsum = A->r + B->r;
+    /* faces of A, then faces of B, in the serial loop order */
+    double best = -INFINITY;
+    int kbest = 0x7fffffff;
+    MG_NOUNROLL
+    for (int f = gl; f < An + Bn; f += PHYS_LANES) {
+        const bool from_a = f < An;
+        const WShape *P = from_a ? A : B, *Q = from_a ? B : A;
+        const int fi = from_a ? f : f - An;
+        const vec2 fn = face_normal(P, fi), pv = P->v[fi];
+        double sep = INFINITY;
+        MG_NOUNROLL
+        for (int j = 0; j < Q->n; j++) {
+            double sj = vdot(vsub(Q->v[j], pv), fn);
+            if (sj < sep) sep = sj;
+        }
+        if (sep > best) { best = sep; kbest = f; }
+    }
+    group_argmax(gmask, best, kbest);
+    const vec2 axis = kbest < An ? face_normal(A, kbest) : vneg(face_normal(B, kbest - An));
+    if (best <= 0.0 || best > rsum) {
+        /* overlapping cores (shallowest face), or too far apart to touch */
+        if (gl == 0 && best - A->r - B->r <= 0.0) contact_points(support_edge(A, axis), support_edge(B, vneg(axis)), axis, best, m);
+        return;
+    }
+    /* closest features: items k = (edge i of A, vertex j of B), then (edge j of B, vertex i of A) */
+    double bestd2 = INFINITY, my_t = 0.0;
+    int kmin = 0x7fffffff;
+    vec2 my_dl = V(0.0, 0.0);
+    const int half = An * Bn;
+    MG_NOUNROLL
+    for (int k = gl; k < 2 * half; k += PHYS_LANES) {
+        vec2 ea, eb, pt;
+        const bool first = k < half;
+        if (first) {
+            const int i = k / Bn, j = k - i * Bn;
+            ea = A->v[(i - 1 + An) % An]; eb = A->v[i]; pt = B->v[j];
+        } else {
+            const int kk = k - half;
+            const int j = kk / An, i = kk - j * An;
+            ea = B->v[(j - 1 + Bn) % Bn]; eb = B->v[j]; pt = A->v[i];
+        }
+        double t;
+        const vec2 q = seg_closest(ea, eb, pt, &t);
+        const vec2 dl = first ? vsub(pt, q) : vsub(q, pt);
+        const double d2 = vdot(dl, dl);
+        if (d2 < bestd2) { bestd2 = d2; kmin = k; my_t = t; my_dl = dl; }
+    }
+    const int my_k = kmin;
+    group_argmin(gmask, bestd2, kmin);
+    if (my_k == kmin && kmin != 0x7fffffff) {
+        vec2 bn; double bd;
+        if (my_t > 0.0 && my_t < 1.0) {
+            bn = kmin < half ? face_normal(A, kmin / Bn) : vneg(face_normal(B, (kmin - half) / An));
+            bd = vdot(my_dl, bn);
+            if (bd < 0.0) { bn = vneg(bn); bd = -bd; }
+        } else {
+            double len = sqrt(bestd2); bd = len; bn = vmul(my_dl, 1.0 / (len + MG_DBL_MIN));
+        }
+        if (bd - A->r - B->r <= 0.0) contact_points(support_edge(A, bn), support_edge(B, vneg(bn)), bn, bd, m);
+    }
+}
+
+/* collide_circle_poly: lane = face, then lane = edge */
+__device__ void coop_circle_poly(const WShape *c, const WShape *p, Manifold *m, int gl, unsigned gmask)
+{
+    const vec2 center = c->v[0];
+    const int n = p->n;
+    double best = -INFINITY;
+    int bi = 0x7fffffff;
+    MG_NOUNROLL
+    for (int i = gl; i < n; i += PHYS_LANES) {
+        double sv = vdot(vsub(center, p->v[i]), p->nrm[i]);
+        if (sv > best) { best = sv; bi = i; }
+    }
+    group_argmax(gmask, best, bi);
+    const double rsum = c->r + p->r;
+    if (best <= 0.0) {
+        if (gl == 0) {
+            vec2 nrm = vneg(p->nrm[bi]);
+            vec2 pb = vsub(center, vmul(p->nrm[bi], best));
+            if (best <= rsum) { m->n = nrm; mf_push(m, vadd(center, vmul(nrm, c->r)), vadd(pb, vmul(nrm, -p->r)), 0); }
+        }
+        return;
+    }
+    if (best > rsum) return;
+    double bestd2 = INFINITY, my_t = 0.0;
+    int imin = 0x7fffffff;
+    vec2 my_dl = V(0.0, 0.0), my_q = center;
+    MG_NOUNROLL
+    for (int i = gl; i < n; i += PHYS_LANES) {
+        double t;
+        const vec2 q = seg_closest(p->v[(i - 1 + n) % n], p->v[i], center, &t);
+        const vec2 dl = vsub(q, center);
+        const double d2 = vdot(dl, dl);
+        if (d2 < bestd2) { bestd2 = d2; imin = i; my_t = t; my_dl = dl; my_q = q; }
+    }
+    const int my_i = imin;
+    group_argmin(gmask, bestd2, imin);
+    if (my_i == imin && imin != 0x7fffffff) {
+        vec2 nrm; double d;
+        if (my_t > 0.0 && my_t < 1.0) { nrm = vneg(p->nrm[imin]); d = vdot(my_dl, nrm); }
+        else { double len = sqrt(bestd2); d = len; nrm = vmul(my_dl, 1.0 / (len + MG_DBL_MIN)); }
+        if (d <= rsum) { m->n = nrm; mf_push(m, vadd(center, vmul(nrm, c->r)), vadd(my_q, vmul(nrm, -p->r)), 0); }
+    }
+}
+
+/* collide_shapes (cpCollide) for the whole group: a->kind <= b->kind; returns the contact count (uniform) */
+__device__ int coop_collide(const WShape *a, const WShape *b, Manifold *m, int gl, unsigned gmask)
+{
+    if (gl == 0) { m->count = 0; m->n = V(0.0, 0.0); }
+    __syncwarp(gmask);
+    if (a->kind == MG_SHAPE_CIRCLE) {
+        if (b->kind == MG_SHAPE_POLY) coop_circle_poly(a, b, m, gl, gmask);
+        else if (gl == 0) { if (b->kind == MG_SHAPE_CIRCLE) collide_circle_circle(a, b, m); else collide_circle_segment(a, b, m); }
+    } else if (!(a->kind == MG_SHAPE_SEGMENT && b->kind == MG_SHAPE_SEGMENT)) {
+        coop_convex_convex(a, b, m, gl, gmask);
+    }
+    __syncwarp(gmask);
+    return m->count;
+}
+
+
+#define NARROW_SLOTS 1
 /* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
 struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
 
@@ -670,7 +840,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
     /* cpBodyUpdatePosition for dynamic and kinematic bodies: lane = body */
     const int nb = IF(e, I_NBODIES);
     MG_NOUNROLL
-    for (int b = 1 + gl; b < nb; b += PHYS_LANES) {
+    for (int b = 1 + gl; b < (PHYS_DBG_SKIP == 6 ? 0 : nb); b += PHYS_LANES) {
         BF(e, b, B_PX) = BF(e, b, B_PX) + (BF(e, b, B_VX) + BF(e, b, B_VBX)) * dt;
         BF(e, b, B_PY) = BF(e, b, B_PY) + (BF(e, b, B_VY) + BF(e, b, B_VBY)) * dt;
         set_angle(e, b, BF(e, b, B_A) + (BF(e, b, B_W) + BF(e, b, B_WB)) * dt);
@@ -685,14 +855,14 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
     const int ns = IF(e, I_NSHAPES);
     /* cpShapeCacheBB once per shape and sub-step (lane = shape): the pair loop below only compares boxes */
     MG_NOUNROLL
-    for (int s = gl; s < ns; s += PHYS_LANES) {
+    for (int s = gl; s < (PHYS_DBG_SKIP == 4 ? 0 : ns); s += PHYS_LANES) {
         const int info = IF(e, I_SHAPE0 + s);
         const int body = (info >> 8) & 255;
         tpl_world_bb(T, info & 255, body_p(e, body), body_rot(e, body), bbs + 4 * s);
     }
     __syncwarp(gmask);
     MG_NOUNROLL
-    for (int i = 0; i + 1 < ns; i++) {
+    for (int i = 0; i + 1 < (PHYS_DBG_SKIP == 3 || PHYS_DBG_SKIP == 4 ? 0 : ns); i++) {
         const int info_i = IF(e, I_SHAPE0 + i);
         const int tpl_i = info_i & 255, body_i = (info_i >> 8) & 255, ent_i = info_i >> 16;
         const double bi0 = bbs[4 * i], bi1 = bbs[4 * i + 1], bi2 = bbs[4 * i + 2], bi3 = bbs[4 * i + 3];
@@ -719,40 +889,39 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
              * double loop discovers them in).  The shapes live in the env's shared scratch: per-lane copies
              * would sit in local memory, which has next to no L1 left beside the env state. */
             unsigned todo = __ballot_sync(gmask, cand);
-            if (todo) {
-                if (lane == __ffs(todo) - 1 && !si_built) wshape_from_tpl(T, tpl_i, body_p(e, body_i), body_rot(e, body_i), &scratch->si);
+            if (PHYS_DBG_SKIP == 8) todo = 0;
+            if (todo && !si_built) {
+                coop_wshape(T, tpl_i, body_p(e, body_i), body_rot(e, body_i), &scratch->si, gl);
                 si_built = true;
-                __syncwarp(gmask);
             }
+            /* the surviving pairs of this row one after the other in j order (the order a serial double loop
+             * discovers them in), each searched by all lanes of the group; a hit goes through cpArbiterUpdate
+             * on the group's first lane */
             while (todo) {
-                const int rank = __popc(todo & ((1u << lane) - 1));          /* among the pending lanes of this group */
-                const bool mine = cand && ((todo >> lane) & 1) && rank < NARROW_SLOTS;
-                bool hit = false, swapped = false;
-                if (mine) {
-                    const int tpl_j = info_j & 255, body_j = (info_j >> 8) & 255;
-                    const WShape *Si = &scratch->si;
-                    WShape *Sj = &scratch->slot[rank].sj;
-                    wshape_from_tpl(T, tpl_j, body_p(e, body_j), body_rot(e, body_j), Sj);
-                    swapped = Si->kind > Sj->kind;           /* cpSpaceCollideShapes orders by cpShapeType */
-                    hit = (swapped ? collide_shapes(Sj, Si, &scratch->slot[rank].mf) : collide_shapes(Si, Sj, &scratch->slot[rank].mf)) != 0;
-                }
-                unsigned hits = __ballot_sync(gmask, hit);
-                while (hits) {
-                    const int src = __ffs(hits) - 1;
-                    hits &= hits - 1;
-                    if (lane == src) {
-                        const Manifold &m = scratch->slot[rank].mf;
-                        int slot = swapped ? arbiter_update(e, j, i, info_j, info_i, m, stamp)
-                                           : arbiter_update(e, i, j, info_i, info_j, m, stamp);
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const int info_s = __shfl_sync(gmask, info_j, src);
+                const int js = j0 + (src & (PHYS_LANES - 1));
+                const int tpl_s = info_s & 255, body_s = (info_s >> 8) & 255;
+                const WShape *Si = &scratch->si;
+                WShape *Sj = &scratch->slot[0].sj;
+                Manifold *mf = &scratch->slot[0].mf;
+                coop_wshape(T, tpl_s, body_p(e, body_s), body_rot(e, body_s), Sj, gl);
+                __syncwarp(gmask);
+                const bool swapped = Si->kind > Sj->kind;            /* cpSpaceCollideShapes orders by cpShapeType */
+                int cnt = swapped ? coop_collide(Sj, Si, mf, gl, gmask) : coop_collide(Si, Sj, mf, gl, gmask);
+                if (PHYS_DBG_SKIP == 9) cnt = 0;
+                if (cnt) {
+                    if (gl == 0) {
+                        int slot = swapped ? arbiter_update(e, js, i, info_s, info_i, *mf, stamp)
+                                           : arbiter_update(e, i, js, info_i, info_s, *mf, stamp);
                         order[MG_NARB] = (unsigned char)(slot >= 0);
                         if (slot >= 0) order[n_live] = (unsigned char)slot;
                     }
                     __syncwarp(gmask);
                     n_live += order[MG_NARB];
-                    __syncwarp(gmask);
                 }
-                /* retire the lanes that ran */
-                todo &= ~__ballot_sync(gmask, mine);
+                __syncwarp(gmask);
             }
         }
     }
@@ -764,10 +933,10 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
     MG_NOUNROLL
     for (int q = gl; q < n_live; q += PHYS_LANES) arb_prestep(e, order[q], slop, bias_c);
     MG_NOUNROLL
-    for (int c = gl; c < nc; c += PHYS_LANES)
+    for (int c = gl; c < (PHYS_DBG_SKIP == 5 ? 0 : nc); c += PHYS_LANES)
         if ((IF(e, I_CON0 + c) & 255) != CON_SPRING) con_prestep(e, c);
     __syncwarp(gmask);
-    return n_live;
+    return PHYS_DBG_SKIP == 7 ? 0 : n_live;
 }
 
 /* ---- the robot's ten constraints with the six robot bodies' velocities in registers.

@@ -38,6 +38,9 @@
 #define WARPS_PER_CTA 4
 #endif
 #define FULL 0xffffffffu
+#ifndef RENDER_PREFETCH
+#define RENDER_PREFETCH 0   /* 1: fetch the next hit's vertices while the current one is painted (measured: no gain) */
+#endif
 
 struct aff { double a, b, tx, c, d, ty; };   /* 3x3 homogeneous matrix, last row 0 0 1 */
 
@@ -533,6 +536,21 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         if (base + lane < np) mine = sprims[base + lane];
         /* outlines reach at most 2 pixels beyond the vertex rows */
         unsigned hits = __ballot_sync(FULL, (mine.off_n & 255) != 0 && mine.maxy + 2 >= y0 && mine.miny - 2 < y0 + BAND_ROWS);
+        /* vertices of the next hit are fetched while the current one is painted (HBM/L2 latency off the serial path) */
+        int2 pre_v[4];
+#define LOAD_VERTS(SRC)                                                                        \
+        {                                                                                      \
+            const int on_ = __shfl_sync(FULL, mine.off_n, (SRC));                              \
+            const int nn_ = on_ & 255;                                                         \
+            const int2 *pv_ = sverts + (on_ >> 8);                                             \
+            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                    \
+                const int i = lane + 32 * k;                                                   \
+                if (i <= nn_) pre_v[k] = pv_[i == nn_ ? 0 : i];                                \
+            }                                                                                  \
+        }
+#if RENDER_PREFETCH
+        if (hits) LOAD_VERTS(__ffs(hits) - 1)
+#endif
       while (hits) {
         const int src = __ffs(hits) - 1;
         hits &= hits - 1;
@@ -541,14 +559,22 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         const uint32_t style = __shfl_sync(FULL, mine.style, src);
         const int n = off_n & 255;
         struct { uint8_t fill, outline, mode, aux; } P = { (uint8_t)style, (uint8_t)(style >> 8), (uint8_t)(style >> 16), (uint8_t)(style >> 24) };
-        const int2 *pv = sverts + (off_n >> 8);
-        for (int i = lane; i < n; i += 32) { int2 v = pv[i]; W->vx[i] = v.x; W->vy[i] = v.y; }
-        if (lane == 0) { int2 v = pv[0]; W->vx[n] = v.x; W->vy[n] = v.y; }
+#if !RENDER_PREFETCH
+        LOAD_VERTS(src)
+#endif
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = lane + 32 * k;
+            if (i <= n) { W->vx[i] = pre_v[k].x; W->vy[i] = pre_v[k].y; }     /* entry n closes the loop */
+        }
         if (P.mode == 2 && lane < 8) {
             double d = S.dashv[A.view][((size_t)env * MG_MAX_GOALS + P.aux) * 8 + lane];
             if (lane & 1) W->fy[lane >> 1] = d; else W->fx[lane >> 1] = d;
         }
         __syncwarp();
+#if RENDER_PREFETCH
+        if (hits) LOAD_VERTS(__ffs(hits) - 1)
+#endif
         {
             if (n <= 8) fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
             else fill_poly_band_edges(W, y0, lane, n, miny, maxy, P.fill);
