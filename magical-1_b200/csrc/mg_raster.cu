@@ -38,6 +38,14 @@
 #define WARPS_PER_CTA 4
 #endif
 #define FULL 0xffffffffu
+#ifndef RENDER_ROLLED
+#define RENDER_ROLLED 1
+#endif
+#if RENDER_ROLLED
+#define RNOUNROLL _Pragma("unroll 1")     /* rolled loops: the kernel is bound by instruction fetch, not by loop overhead */
+#else
+#define RNOUNROLL
+#endif
 #ifndef RENDER_PREFETCH
 #define RENDER_PREFETCH 0   /* 1: fetch the next hit's vertices while the current one is painted (measured: no gain) */
 #endif
@@ -191,6 +199,7 @@ __device__ void draw_line_warp(uint8_t *buf, int y0, int lane, int x1, int y1, i
     if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
     Line L;
     if (!line_setup(x1, y1, x2, y2, L)) return;
+    RNOUNROLL
     for (int k = lane; k < L.len; k += 32) {
         int x, y;
         line_pixel(L, k, x, y);
@@ -203,6 +212,7 @@ __device__ void draw_line_lane(uint8_t *buf, int y0, int x1, int y1, int x2, int
     if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
     Line L;
     if (!line_setup(x1, y1, x2, y2, L)) return;
+    RNOUNROLL
     for (int k = 0; k < L.len; k++) {
         int x, y;
         line_pixel(L, k, x, y);
@@ -249,6 +259,7 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
     }
     int n_dash = n / 2;
     /* lane = (dash, copy) */
+    RNOUNROLL
     for (int job = lane; job < n_dash * 4; job += 32) {
         int d = job >> 2, copy = job & 3;
         double xa = sx_ != 0 ? arange_at(x1, sx_, 2 * d + 1) : x1, ya = sy_ != 0 ? arange_at(y1, sy_, 2 * d + 1) : y1;
@@ -276,11 +287,16 @@ __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t 
     }
     const uint32_t c4 = c * 0x01010101u;
     int x = lo;
+    RNOUNROLL
     while (x <= hi && (x & 3)) row[x++] = c;
+    RNOUNROLL
     while (x + 3 <= hi && (x & 15)) { *(uint32_t *)(row + x) = c4; x += 4; }
     const uint4 c16 = make_uint4(c4, c4, c4, c4);
+    RNOUNROLL
     for (; x + 15 <= hi; x += 16) *(uint4 *)(row + x) = c16;
+    RNOUNROLL
     for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
+    RNOUNROLL
     for (; x <= hi; x++) row[x] = c;
 }
 
@@ -293,9 +309,11 @@ __device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, i
     int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
     if (miny == maxy) {
         /* polygon one pixel high: span = x extent */
+        RNOUNROLL
         for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
         cnt = 2;
     } else {
+        RNOUNROLL
         for (int i = 0; i < n; i++) {
             int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
             int x1, y1, x2, y2;
@@ -321,11 +339,13 @@ __device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int m
     __syncwarp();
     if (miny == maxy) {
         int lo = 0x7fffffff, hi = -0x7fffffff - 1;
+        RNOUNROLL
         for (int i = lane; i < n; i += 32) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
         lo = __reduce_min_sync(FULL, lo); hi = __reduce_max_sync(FULL, hi);
         unsigned r = (unsigned)(miny - y0);
         if (r == (unsigned)lane && lane < BAND_ROWS) { W->span_lo[lane] = lo; W->span_hi[lane] = hi; W->span_cnt[lane] = 2; }
     } else {
+        RNOUNROLL
         for (int i = lane; i < n; i += 32) {
             int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
             int x1, y1, x2, y2;
@@ -336,6 +356,7 @@ __device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int m
             int ylast = y2 == maxy ? y2 : y2 - 1;
             int ya_ = max(y1, y0), yb_ = min(ylast, y0 + BAND_ROWS - 1);
             float rb = __frcp_rn((float)(y2 - y1));
+            RNOUNROLL
             for (int y = ya_; y <= yb_; y++) {
                 int num = (y - y1) * (x2 - x1);
                 int x = (num >= 0 ? div_small(num, y2 - y1, rb) : -div_small(-num, y2 - y1, rb)) + x1;
@@ -522,6 +543,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     {
         const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
         const uint4 bg16 = make_uint4(bg4, bg4, bg4, bg4);
+        RNOUNROLL
         for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 16; i += 32) ((uint4 *)W->buf)[i] = bg16;
     }
     __syncwarp();
@@ -582,6 +604,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             if (P.mode == 1) {
                 /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
                 if (n <= 8) {
+                    RNOUNROLL
                     for (int i = 0; i < n; i++)
                         for (int copy = 0; copy < 2; copy++) {
                             int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
@@ -589,6 +612,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                             draw_line_warp(W->buf, y0, lane, x1, y1, x2, y2, P.outline);
                         }
                 } else {
+                    RNOUNROLL
                     for (int job = lane; job < 2 * n; job += 32) {
                         int i = job >> 1, copy = job & 1;
                         int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
@@ -597,6 +621,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                     }
                 }
             } else if (P.mode == 2) {
+                RNOUNROLL
                 for (int i = 0; i < n; i++) {
                     int j = (i + 1) % n;
                     draw_dashed_edge(W->buf, y0, lane, W->fx[i], W->fy[i], W->fx[j], W->fy[j], P.outline);
@@ -653,6 +678,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now */
         const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
         int n_mixed = 0;
+        RNOUNROLL
         for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {       /* 768 = 24 full warps of blocks */
             int oy = o / MG_LORES, ox = o % MG_LORES;
             const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
@@ -674,6 +700,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         }
         __syncwarp();
         n_mixed = min(n_mixed, MIXED_MAX);
+        RNOUNROLL
         for (int k = lane; k < n_mixed; k += 32) {
             int o = mixed[k];
             int oy = o / MG_LORES, ox = o % MG_LORES;
@@ -690,6 +717,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     const size_t band_off = (size_t)band * LO_BAND_BYTES;
     if (MODE == 1) {
         uint4 *dst = (uint4 *)(A.out + (size_t)env * MG_FRAME_BYTES + band_off);
+        RNOUNROLL
         for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
         return;
     }
@@ -697,9 +725,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     /* mode 0: push into the frame ring.  A freshly reset env fills every slot with its first
      * frame (FlattenFrameStack.reset / EagerDictFrameStack.reset, benchmarks/__init__.py:66-74, 139-147) */
     uint8_t *ring = S.ring[A.view] + (size_t)env * MG_MAX_RING * MG_FRAME_BYTES;
+    RNOUNROLL
     for (int s = 0; s < MG_MAX_RING; s++) {
         if (!fresh && s != A.slot) continue;
         uint4 *dst = (uint4 *)(ring + (size_t)s * MG_FRAME_BYTES + band_off);
+        RNOUNROLL
         for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
     }
     if (VARIANT == 0) return;
