@@ -193,30 +193,41 @@ __device__ __forceinline__ void put_px(uint8_t *buf, int y0, int x, int y, uint8
 /* offsets of clip_and_draw_line_width: width 2 -> 0,+1; width 4 -> 0,+1,-1,+2 */
 __device__ __forceinline__ int width_offset(int copy) { return copy == 0 ? 0 : (copy == 1 ? 1 : (copy == 2 ? -1 : 2)); }
 
-/* all pixels of one line copy, pixels spread over the lanes of the warp */
-__device__ void draw_line_warp(uint8_t *buf, int y0, int lane, int x1, int y1, int x2, int y2, uint8_t c)
+/* One batch of up to 32 line copies, lane = job (has == false: no job).  Every lane clips and sets up its own line;
+ * lines longer than LONG_LINE pixels are then handed to the whole warp one after the other (pixels spread over the
+ * lanes), the short ones are drawn by their own lanes side by side.  All copies of one outline carry the same
+ * colour, so the order in which their pixels land does not matter.  The only copy of the line code in the kernel
+ * (the kernel is bound by instruction fetch). */
+#define LONG_LINE 12
+__device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool has, int x1, int y1, int x2, int y2, uint8_t c)
 {
-    if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
-    Line L;
-    if (!line_setup(x1, y1, x2, y2, L)) return;
-    RNOUNROLL
-    for (int k = lane; k < L.len; k += 32) {
-        int x, y;
-        line_pixel(L, k, x, y);
-        put_px(buf, y0, x, y, c);
+    Line L = { 0, 0, 1, 1, 1, 1, 0, true, 1.0f };      /* len 0: nothing to draw */
+    if (has && !(max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS)) line_setup(x1, y1, x2, y2, L);   /* sets len only if the clip keeps the line */
+    unsigned longs = __ballot_sync(FULL, L.len > LONG_LINE);
+    const int packed = (L.sx & 3) | (L.sy & 3) << 2 | (int)L.xmajor << 4;
+    while (longs) {
+        const int src = __ffs(longs) - 1;
+        longs &= longs - 1;
+        Line M;
+        M.x1 = __shfl_sync(FULL, L.x1, src); M.y1 = __shfl_sync(FULL, L.y1, src);
+        M.dxp = __shfl_sync(FULL, L.dxp, src); M.dyp = __shfl_sync(FULL, L.dyp, src);
+        M.len = __shfl_sync(FULL, L.len, src); M.rmaj = __shfl_sync(FULL, L.rmaj, src);
+        const int pk = __shfl_sync(FULL, packed, src);
+        M.sx = (pk & 3) == 1 ? 1 : -1; M.sy = ((pk >> 2) & 3) == 1 ? 1 : -1; M.xmajor = (pk >> 4) & 1;
+        RNOUNROLL
+        for (int k = lane; k < M.len; k += 32) {
+            int x, y;
+            line_pixel(M, k, x, y);
+            put_px(buf, y0, x, y, c);
+        }
     }
-}
-/* all pixels of one line copy, drawn by the calling lane alone */
-__device__ void draw_line_lane(uint8_t *buf, int y0, int x1, int y1, int x2, int y2, uint8_t c)
-{
-    if (max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS) return;
-    Line L;
-    if (!line_setup(x1, y1, x2, y2, L)) return;
-    RNOUNROLL
-    for (int k = 0; k < L.len; k++) {
-        int x, y;
-        line_pixel(L, k, x, y);
-        put_px(buf, y0, x, y, c);
+    if (L.len <= LONG_LINE) {
+        RNOUNROLL
+        for (int k = 0; k < L.len; k++) {
+            int x, y;
+            line_pixel(L, k, x, y);
+            put_px(buf, y0, x, y, c);
+        }
     }
 }
 
@@ -260,14 +271,16 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
     int n_dash = n / 2;
     /* lane = (dash, copy) */
     RNOUNROLL
-    for (int job = lane; job < n_dash * 4; job += 32) {
+    for (int job0 = 0; job0 < n_dash * 4; job0 += 32) {
+        const int job = job0 + lane;
+        const bool has = job < n_dash * 4;
         int d = job >> 2, copy = job & 3;
         double xa = sx_ != 0 ? arange_at(x1, sx_, 2 * d + 1) : x1, ya = sy_ != 0 ? arange_at(y1, sy_, 2 * d + 1) : y1;
         double xb = sx_ != 0 ? arange_at(x1, sx_, 2 * d) : x1, yb = sy_ != 0 ? arange_at(y1, sy_, 2 * d) : y1;
         int px1 = (int)rint(xa), py1 = (int)rint(ya), px2 = (int)rint(xb), py2 = (int)rint(yb);
         int off = width_offset(copy);
         if (abs(px1 - px2) > abs(py1 - py2)) { py1 += off; py2 += off; } else { px1 += off; px2 += off; }
-        draw_line_lane(buf, y0, px1, py1, px2, py2, c);
+        draw_line_jobs(buf, y0, lane, has, px1, py1, px2, py2, c);
     }
 }
 
@@ -603,22 +616,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             __syncwarp();
             if (P.mode == 1) {
                 /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
-                if (n <= 8) {
-                    RNOUNROLL
-                    for (int i = 0; i < n; i++)
-                        for (int copy = 0; copy < 2; copy++) {
-                            int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
-                            if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
-                            draw_line_warp(W->buf, y0, lane, x1, y1, x2, y2, P.outline);
-                        }
-                } else {
-                    RNOUNROLL
-                    for (int job = lane; job < 2 * n; job += 32) {
-                        int i = job >> 1, copy = job & 1;
-                        int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
-                        if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
-                        draw_line_lane(W->buf, y0, x1, y1, x2, y2, P.outline);
-                    }
+                RNOUNROLL
+                for (int job0 = 0; job0 < 2 * n; job0 += 32) {
+                    const int job = job0 + lane;
+                    const bool has = job < 2 * n;
+                    const int i = has ? job >> 1 : 0, copy = job & 1;
+                    int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
+                    if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
+                    draw_line_jobs(W->buf, y0, lane, has, x1, y1, x2, y2, P.outline);
                 }
             } else if (P.mode == 2) {
                 RNOUNROLL
