@@ -313,50 +313,20 @@ __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t 
     for (; x <= hi; x++) row[x] = c;
 }
 
-/* pygame.draw.polygon fill of rows [y0, y0 + BAND_ROWS): lane owns row y0 + lane % BAND_ROWS */
-__device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
-{
-    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
-    int y = y0 + row;
-    if (y < miny || y > maxy) return;
-    int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
-    if (miny == maxy) {
-        /* polygon one pixel high: span = x extent */
-        RNOUNROLL
-        for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
-        cnt = 2;
-    } else {
-        RNOUNROLL
-        for (int i = 0; i < n; i++) {
-            int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
-            int x1, y1, x2, y2;
-            if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
-            else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
-            else continue;
-            if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
-                int x = div_trunc((y - y1) * (x2 - x1), y2 - y1) + x1;
-                lo = min(lo, x); hi = max(hi, x); cnt++;
-            }
-        }
-    }
-    if (cnt < 2) return;
-    fill_span(W->buf + row * ROW_STRIDE, lo, hi, c, part);
-}
-
 /* same fill for polygons with many edges (the 100-gon circles): lanes take edges, every edge adds its
  * crossings to the rows of the band it spans; then the row's lanes fill it.  Same spans as the row-parallel form. */
-__device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
+__device__ __forceinline__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, int &lo, int &hi, int &cnt)
 {
-    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
+    const int row = lane % BAND_ROWS;
     if (lane < BAND_ROWS) { W->span_lo[lane] = 0x7fffffff; W->span_hi[lane] = -0x7fffffff - 1; W->span_cnt[lane] = 0; }
     __syncwarp();
     if (miny == maxy) {
-        int lo = 0x7fffffff, hi = -0x7fffffff - 1;
+        int xlo = 0x7fffffff, xhi = -0x7fffffff - 1;
         RNOUNROLL
-        for (int i = lane; i < n; i += 32) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
-        lo = __reduce_min_sync(FULL, lo); hi = __reduce_max_sync(FULL, hi);
+        for (int i = lane; i < n; i += 32) { xlo = min(xlo, W->vx[i]); xhi = max(xhi, W->vx[i]); }
+        xlo = __reduce_min_sync(FULL, xlo); xhi = __reduce_max_sync(FULL, xhi);
         unsigned r = (unsigned)(miny - y0);
-        if (r == (unsigned)lane && lane < BAND_ROWS) { W->span_lo[lane] = lo; W->span_hi[lane] = hi; W->span_cnt[lane] = 2; }
+        if (r == (unsigned)lane && lane < BAND_ROWS) { W->span_lo[lane] = xlo; W->span_hi[lane] = xhi; W->span_cnt[lane] = 2; }
     } else {
         RNOUNROLL
         for (int i = lane; i < n; i += 32) {
@@ -380,7 +350,38 @@ __device__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int m
         }
     }
     __syncwarp();
-    if (W->span_cnt[row] >= 2) fill_span(W->buf + row * ROW_STRIDE, W->span_lo[row], W->span_hi[row], c, part);
+    lo = W->span_lo[row]; hi = W->span_hi[row]; cnt = W->span_cnt[row];
+}
+
+/* pygame.draw.polygon fill of rows [y0, y0 + BAND_ROWS): lane owns row y0 + lane % BAND_ROWS */
+__device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
+{
+    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
+    int y = y0 + row;
+    int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
+    if (n > 8) fill_poly_band_edges(W, y0, lane, n, miny, maxy, lo, hi, cnt);
+    else if (y < miny || y > maxy) cnt = 0;
+    else if (miny == maxy) {
+        /* polygon one pixel high: span = x extent */
+        RNOUNROLL
+        for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
+        cnt = 2;
+    } else {
+        RNOUNROLL
+        for (int i = 0; i < n; i++) {
+            int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
+            int x1, y1, x2, y2;
+            if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
+            else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
+            else continue;
+            if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
+                int x = div_trunc((y - y1) * (x2 - x1), y2 - y1) + x1;
+                lo = min(lo, x); hi = max(hi, x); cnt++;
+            }
+        }
+    }
+    if (cnt < 2) return;
+    fill_span(W->buf + row * ROW_STRIDE, lo, hi, c, part);
 }
 
 __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3)
@@ -611,8 +612,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         if (hits) LOAD_VERTS(__ffs(hits) - 1)
 #endif
         {
-            if (n <= 8) fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
-            else fill_poly_band_edges(W, y0, lane, n, miny, maxy, P.fill);
+            fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
             __syncwarp();
             if (P.mode == 1) {
                 /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
@@ -683,31 +683,36 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now */
         const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
         int n_mixed = 0;
-        RNOUNROLL
-        for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {       /* 768 = 24 full warps of blocks */
-            int oy = o / MG_LORES, ox = o % MG_LORES;
-            const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
-            uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
-            uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
-            bool mix = !(w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u);
-            unsigned m = __ballot_sync(FULL, mix);
-            uint32_t rgb = pal[w0 & 31];
-            if (mix) {
-                int idx = n_mixed + __popc(m & ((1u << lane) - 1));
-                if (idx < MIXED_MAX) mixed[idx] = (uint16_t)o;
-                else { rgb = pal_sum16(pal, w0, w1, w2, w3); mix = false; }
-            }
-            n_mixed += __popc(m);
-            if (!mix) {
-                uint8_t *d = W->lo + o * 3;
+        {
+            /* block o = lane + 32 it: pointers advance by a constant, wrapping to the next block row every 96 */
+            const uint8_t *base = W->buf + 4 * lane;
+            uint8_t *d = W->lo + 3 * lane;
+            int ox = lane;
+            const unsigned lt_mask = (1u << lane) - 1;
+            RNOUNROLL
+            for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {   /* 768 = 24 full warps of blocks */
+                const uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
+                const uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
+                const bool mix = !(w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u);
+                const unsigned m = __ballot_sync(FULL, mix);
+                const uint32_t rgb = pal[w0 & 31];           /* right for a one-colour block; mixed ones are redone below */
+                if (mix) {
+                    const int idx = n_mixed + __popc(m & lt_mask);
+                    if (idx < MIXED_MAX) mixed[idx] = (uint16_t)o;
+                }
+                n_mixed += __popc(m);
                 d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+                d += 96; ox += 32; base += 128;
+                if (ox >= MG_LORES) { ox -= MG_LORES; base += 4 * ROW_STRIDE - 4 * MG_LORES; }
             }
         }
         __syncwarp();
-        n_mixed = min(n_mixed, MIXED_MAX);
+        /* more mixed blocks than the queue holds (never seen with the reference's scenes): sum every block */
+        const bool all_blocks = n_mixed > MIXED_MAX;
+        if (all_blocks) n_mixed = LO_ROWS * MG_LORES;
         RNOUNROLL
         for (int k = lane; k < n_mixed; k += 32) {
-            int o = mixed[k];
+            int o = all_blocks ? k : mixed[k];
             int oy = o / MG_LORES, ox = o % MG_LORES;
             const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
             uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
