@@ -204,7 +204,22 @@ __device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool
 {
     Line L = { 0, 0, 1, 1, 1, 1, 0, true, 1.0f };      /* len 0: nothing to draw */
     if (has && !(max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS)) line_setup(x1, y1, x2, y2, L);   /* sets len only if the clip keeps the line */
-    unsigned longs = __ballot_sync(FULL, L.len > LONG_LINE);
+    /* pixels k0 .. k1 of the line can fall into this band: a superset (put_px still tests the row), so the picture
+     * is the same, but a long steep line costs a band only its own rows instead of its whole length */
+    int k0 = 0, k1 = L.len - 1;
+    if (L.len > 0) {
+        /* minor-axis (x-major) or pixel (y-major) index range whose row lies in [y0, y0 + BAND_ROWS) */
+        int ta = (y0 - L.y1) * L.sy, tb = (y0 + BAND_ROWS - 1 - L.y1) * L.sy;
+        if (ta > tb) { int t = ta; ta = tb; tb = t; }
+        if (!L.xmajor) { k0 = max(k0, ta); k1 = min(k1, tb); }
+        else if (L.dyp > 1) {
+            const float r = (float)L.dxp * __frcp_rn((float)L.dyp);
+            k0 = max(k0, (int)((float)max(ta, 0) * r) - 2);
+            k1 = min(k1, (int)((float)(min(tb, L.dyp) + 1) * r) + 2);
+        }
+    }
+    const int cnt = k1 - k0 + 1;
+    unsigned longs = __ballot_sync(FULL, cnt > LONG_LINE);
     const int packed = (L.sx & 3) | (L.sy & 3) << 2 | (int)L.xmajor << 4;
     while (longs) {
         const int src = __ffs(longs) - 1;
@@ -212,19 +227,20 @@ __device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool
         Line M;
         M.x1 = __shfl_sync(FULL, L.x1, src); M.y1 = __shfl_sync(FULL, L.y1, src);
         M.dxp = __shfl_sync(FULL, L.dxp, src); M.dyp = __shfl_sync(FULL, L.dyp, src);
-        M.len = __shfl_sync(FULL, L.len, src); M.rmaj = __shfl_sync(FULL, L.rmaj, src);
+        M.rmaj = __shfl_sync(FULL, L.rmaj, src);
+        const int m0 = __shfl_sync(FULL, k0, src), m1 = __shfl_sync(FULL, k1, src);
         const int pk = __shfl_sync(FULL, packed, src);
         M.sx = (pk & 3) == 1 ? 1 : -1; M.sy = ((pk >> 2) & 3) == 1 ? 1 : -1; M.xmajor = (pk >> 4) & 1;
         RNOUNROLL
-        for (int k = lane; k < M.len; k += 32) {
+        for (int k = m0 + lane; k <= m1; k += 32) {
             int x, y;
             line_pixel(M, k, x, y);
             put_px(buf, y0, x, y, c);
         }
     }
-    if (L.len <= LONG_LINE) {
+    if (cnt <= LONG_LINE) {
         RNOUNROLL
-        for (int k = 0; k < L.len; k++) {
+        for (int k = k0; k <= k1; k++) {
             int x, y;
             line_pixel(L, k, x, y);
             put_px(buf, y0, x, y, c);
