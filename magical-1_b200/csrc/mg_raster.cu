@@ -48,7 +48,7 @@
 #define RNOUNROLL
 #endif
 #ifndef RENDER_PREFETCH
-#define RENDER_PREFETCH 0   /* 1: fetch the next hit's vertices while the current one is painted (measured: no gain) */
+#define RENDER_PREFETCH 1   /* fetch the next hit's vertices while the current one is painted */
 #endif
 
 struct aff { double a, b, tx, c, d, ty; };   /* 3x3 homogeneous matrix, last row 0 0 1 */
@@ -570,6 +570,15 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
     }
+    /* primitives in draw order, 32 headers per coalesced load; each lane tests its own primitive against
+     * the band and the warp then walks the hits in order (painter's algorithm) */
+    const MgScreenPrim *sprims = S.sprims[A.view] + (size_t)env * MG_MAX_PRIMS;
+    const int2 *sverts = S.sverts[A.view] + (size_t)env * MG_MAX_VERTS;
+    const int np = S.n_prims[env];
+    /* the first 32 headers are on their way while the background is filled */
+    const MgScreenPrim no_prim = { 0, 0x7fffffff, -0x7fffffff - 1, 0 };
+    MgScreenPrim first = no_prim;
+    if (lane < np) first = sprims[lane];
     /* Viewer._clear: background */
     {
         const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
@@ -579,14 +588,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     }
     __syncwarp();
 
-    /* primitives in draw order, 32 headers per coalesced load; each lane tests its own primitive against
-     * the band and the warp then walks the hits in order (painter's algorithm) */
-    const MgScreenPrim *sprims = S.sprims[A.view] + (size_t)env * MG_MAX_PRIMS;
-    const int2 *sverts = S.sverts[A.view] + (size_t)env * MG_MAX_VERTS;
-    const int np = S.n_prims[env];
     for (int base = 0; base < np; base += 32) {
-        MgScreenPrim mine = { 0, 0x7fffffff, -0x7fffffff - 1, 0 };
-        if (base + lane < np) mine = sprims[base + lane];
+        MgScreenPrim mine = base == 0 ? first : no_prim;
+        if (base > 0 && base + lane < np) mine = sprims[base + lane];
         /* outlines reach at most 2 pixels beyond the vertex rows */
         unsigned hits = __ballot_sync(FULL, (mine.off_n & 255) != 0 && mine.maxy + 2 >= y0 && mine.miny - 2 < y0 + BAND_ROWS);
         /* vertices of the next hit are fetched while the current one is painted (HBM/L2 latency off the serial path) */
