@@ -705,26 +705,33 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
         int n_mixed = 0;
         {
-            /* block o = lane + 32 it: pointers advance by a constant, wrapping to the next block row every 96 */
-            const uint8_t *base = W->buf + 4 * lane;
-            uint8_t *d = W->lo + 3 * lane;
-            int ox = lane;
+            /* a lane takes four neighbouring blocks: four 16-byte loads in, three words (4 x RGB) out; quad
+             * q = lane + 32 it, 24 quads per block row */
             const unsigned lt_mask = (1u << lane) - 1;
+            uint32_t *lo_w = (uint32_t *)W->lo;
             RNOUNROLL
-            for (int o = lane; o < LO_ROWS * MG_LORES; o += 32) {   /* 768 = 24 full warps of blocks */
-                const uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
-                const uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
-                const bool mix = !(w0 == w1 && w0 == w2 && w0 == w3 && w0 == (w0 & 255) * 0x01010101u);
-                const unsigned m = __ballot_sync(FULL, mix);
-                const uint32_t rgb = pal[w0 & 31];           /* right for a one-colour block; mixed ones are redone below */
-                if (mix) {
-                    const int idx = n_mixed + __popc(m & lt_mask);
-                    if (idx < MIXED_MAX) mixed[idx] = (uint16_t)o;
+            for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads */
+                const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
+                const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
+                const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
+                const uint4 r2 = *(const uint4 *)(base + 2 * ROW_STRIDE), r3 = *(const uint4 *)(base + 3 * ROW_STRIDE);
+                const uint32_t w0[4] = { r0.x, r0.y, r0.z, r0.w }, w1[4] = { r1.x, r1.y, r1.z, r1.w };
+                const uint32_t w2[4] = { r2.x, r2.y, r2.z, r2.w }, w3[4] = { r3.x, r3.y, r3.z, r3.w };
+                uint32_t rgb[4];
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    const bool mix = !(w0[b] == w1[b] && w0[b] == w2[b] && w0[b] == w3[b] && w0[b] == (w0[b] & 255) * 0x01010101u);
+                    rgb[b] = pal[w0[b] & 31];                /* right for a one-colour block; mixed ones are redone below */
+                    const unsigned m = __ballot_sync(FULL, mix);
+                    if (mix) {
+                        const int idx = n_mixed + __popc(m & lt_mask);
+                        if (idx < MIXED_MAX) mixed[idx] = (uint16_t)(oy * MG_LORES + 4 * ox4 + b);
+                    }
+                    n_mixed += __popc(m);
                 }
-                n_mixed += __popc(m);
-                d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
-                d += 96; ox += 32; base += 128;
-                if (ox >= MG_LORES) { ox -= MG_LORES; base += 4 * ROW_STRIDE - 4 * MG_LORES; }
+                lo_w[3 * q] = rgb[0] | rgb[1] << 24;
+                lo_w[3 * q + 1] = rgb[1] >> 8 | rgb[2] << 16;
+                lo_w[3 * q + 2] = rgb[2] >> 16 | rgb[3] << 8;
             }
         }
         __syncwarp();
