@@ -702,7 +702,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
      * second, dense pass so that one mixed block does not drag its 31 neighbours through the slow path. */
     {
         uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now */
+#ifdef MG_TEST_MIXED_MAX
+        const int MIXED_MAX = MG_TEST_MIXED_MAX;                   /* test builds: force the every-block fallback below */
+#else
         const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
+#endif
         int n_mixed = 0;
         {
             /* a lane takes four neighbouring blocks: four 16-byte loads in, three words (4 x RGB) out; quad
