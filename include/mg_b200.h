@@ -92,7 +92,11 @@ int mg_reset_obs(mg_handle *h, uint8_t *obs_dev, void *stream);
 
 /* One env-step for all envs: action decode, 10 physics sub-steps, horizon/score, render,
  * 4x area downsample, frame stack.  reward/done/score may be NULL.
- * score_dev receives info['eval_score'] (0 until the last step of the episode). */
+ * score_dev receives info['eval_score'] (0 until the last step of the episode).
+ * For single-view HWC stacks the batch is cut into parts on internal streams (forked from and joined back to
+ * `stream`), so that the rendering of finished parts runs under the tail of the physics of the others; the
+ * results are those of mg_step_physics followed by mg_step_render.  While mg_set_timing is on, or with
+ * MG_STEP_PARTS=1 in the environment, the plain sequence runs. */
 int mg_step(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev,
             uint8_t *done_dev, float *score_dev, void *stream);
 

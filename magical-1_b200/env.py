@@ -257,6 +257,12 @@ class BatchedMagicalEnv:
             self._actions.copy_(torch.from_numpy(a.astype(np.int32)), non_blocking=False)
             actions = self._actions
         st = self._stream()
+        if self._obs is not None and not (self.auto_reset and (self._episode_steps + 1 >= self._horizons).any()):
+            # no env finishes on this step: the one-call step (render of finished parts under the physics tail)
+            self._check(self._lib.mg_step(self._h, L.ptr(actions), L.ptr(self._obs), L.ptr(self._reward), L.ptr(self._done),
+                                          L.ptr(self._score), st))
+            self._episode_steps += 1
+            return self._make_obs(), self._reward, self._done.bool(), {'eval_score': self._score}
         self._check(self._lib.mg_step_physics(self._h, L.ptr(actions), L.ptr(self._reward), L.ptr(self._done),
                                               L.ptr(self._score), st))
         self._episode_steps += 1

@@ -382,3 +382,32 @@ def test_step_host_matches_device_step(preproc, n_envs):
         np.testing.assert_array_equal(rew_h.numpy(), rew.cpu().numpy())
         np.testing.assert_array_equal(done_h.numpy().astype(bool), done.cpu().numpy())
     a.close(); b.close()
+
+
+@pytest.mark.gpu
+def test_step_in_parts_equals_plain_sequence(monkeypatch):
+    """mg_step cuts the batch into parts on internal streams (render of finished parts under the physics tail of the
+    others): observations, rewards, scores and body states equal those of the plain physics -> render sequence."""
+    import torch
+    import magical_b200 as m
+    B, T = 1024, 45
+    acts = np.random.RandomState(3).randint(0, 18, size=(T, B))
+    outs = []
+    for parts in ('1', '4', '13'):
+        monkeypatch.setenv('MG_STEP_PARTS', parts)
+        env = m.make('FindDupe-TestLayout-LoRes4E-v0', num_envs=B, seed=5, obs_keys=('past_obs',))
+        env.auto_reset = False
+        env.reset()
+        launches0 = env.launch_count()
+        rews = []
+        for t in range(T):
+            obs, rew, done, info = env.step(acts[t])
+            rews.append(rew.clone())
+        torch.cuda.synchronize()
+        outs.append((obs['past_obs'].clone(), torch.stack(rews), info['eval_score'].clone(), env.get_bodies(),
+                     env.launch_count() - launches0))
+        env.close()
+    assert outs[1][4] > outs[0][4] and outs[2][4] > outs[1][4]        # the parts really ran as separate launches
+    for o in outs[1:]:
+        assert torch.equal(o[0], outs[0][0]) and torch.equal(o[1], outs[0][1]) and torch.equal(o[2], outs[0][2])
+        assert (o[3] == outs[0][3]).all()
