@@ -36,6 +36,8 @@ struct mg_handle {
     cudaStream_t part_stream[MG_STEP_PARTS];   /* mg_step: one stream per part of the batch (render of a part under the physics of the others) */
     cudaEvent_t part_done[MG_STEP_PARTS], fork_ev;
     int step_parts;                          /* 0/1: plain sequence */
+    int step_order;                          /* group the envs of a part by contact load (mg_order_kernel) */
+    int *perm_dev;                           /* [B] env order of the current mg_step */
     cudaEvent_t chunk_done[MG_HOST_CHUNKS];
     /* accounting */
     int64_t launches;
@@ -140,6 +142,9 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
         h->step_parts = ev ? atoi(ev) : cfg->num_envs / 256;
         if (!ev && h->step_parts > 16) h->step_parts = 16;
         if (h->step_parts > MG_STEP_PARTS) h->step_parts = MG_STEP_PARTS;
+        const char *eo = getenv("MG_STEP_ORDER");
+        h->step_order = eo ? atoi(eo) : 1;
+        CK(h, cudaMalloc(&h->perm_dev, (size_t)cfg->num_envs * sizeof(int)));
     }
     *out = h;
     return MG_OK;
@@ -159,6 +164,7 @@ extern "C" int mg_destroy(mg_handle *h)
     for (int c = 0; c < MG_HOST_CHUNKS; c++) cudaEventDestroy(h->chunk_done[c]);
     for (int c = 0; c < MG_STEP_PARTS; c++) { cudaStreamDestroy(h->part_stream[c]); cudaEventDestroy(h->part_done[c]); }
     cudaEventDestroy(h->fork_ev);
+    cudaFree(h->perm_dev);
     for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (auto e : h->free_events) cudaEventDestroy(e);
     delete h;
@@ -268,6 +274,10 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
     const int B = h->cfg.num_envs, P = h->step_parts;
     int view = -1;
     for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); view = v; }
+    /* envs without contacts take a third of the time of an env wedged into a corner, and a CTA (a part) is as slow as
+     * its slowest env: order the envs by contact load so that the light parts finish, and render, early */
+    const bool ordered = h->step_order != 0;
+    if (ordered) mg_launch_order(h->S, h->perm_dev, st);
     CK(h, cudaEventRecord(h->fork_ev, st));
     int lo[MG_STEP_PARTS + 1];
     for (int k = 0; k <= P; k++) lo[k] = k == P ? B : (int)((long long)B * k / P) & ~31;   /* whole CTAs of 16 / 8 envs */
@@ -276,18 +286,25 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
         CK(h, cudaStreamWaitEvent(sk, h->fork_ev, 0));
         MgDeviceState Sk = h->S;
         Sk.num_envs = lo[k + 1] - lo[k];
-        Sk.dstate += (size_t)lo[k] * D_NF; Sk.istate += (size_t)lo[k] * I_NF; Sk.poses += (size_t)lo[k] * MG_POSE_STRIDE;
-        mg_launch_physics(Sk, actions_dev + lo[k], reward_dev ? reward_dev + lo[k] : nullptr, done_dev ? done_dev + lo[k] : nullptr,
-                          score_dev ? score_dev + lo[k] : nullptr, h->max_blocks, sk);
+        if (ordered) {
+            Sk.perm = h->perm_dev + lo[k];
+            mg_launch_physics(Sk, actions_dev, reward_dev, done_dev, score_dev, h->max_blocks, sk);
+        } else {
+            Sk.dstate += (size_t)lo[k] * D_NF; Sk.istate += (size_t)lo[k] * I_NF; Sk.poses += (size_t)lo[k] * MG_POSE_STRIDE;
+            mg_launch_physics(Sk, actions_dev + lo[k], reward_dev ? reward_dev + lo[k] : nullptr, done_dev ? done_dev + lo[k] : nullptr,
+                              score_dev ? score_dev + lo[k] : nullptr, h->max_blocks, sk);
+        }
     }
     for (int k = 0; k < P; k++) {
         cudaStream_t sk = h->part_stream[k];
-        mg_launch_render_push(h->S, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk);
+        MgDeviceState Sr = h->S;
+        if (ordered) Sr.perm = h->perm_dev;
+        mg_launch_render_push(Sr, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk);
         CK(h, cudaEventRecord(h->part_done[k], sk));
         CK(h, cudaStreamWaitEvent(st, h->part_done[k], 0));
     }
     mg_launch_clear_fresh(h->S, st);
-    h->launches += 3 * P + 1;
+    h->launches += 3 * P + 1 + (ordered ? 1 : 0);
     return check_launch(h, "mg_step (parts)");
 }
 

@@ -26,6 +26,9 @@ struct MgDeviceState {
     MgScreenPrim *sprims[2]; /* [B][MG_MAX_PRIMS] */
     int2 *sverts[2];         /* [B][MG_MAX_VERTS] truncated vertices */
     double *dashv[2];        /* [B][MG_MAX_GOALS][4][2] untruncated goal-region vertices (dashed outlines) */
+    /* optional order of the envs for this launch (NULL = identity): the step and render kernels take env perm[k] for
+     * their k-th work slot, so that a part of the batch can be any set of envs (mg_step groups envs by contact load) */
+    const int *perm;
 };
 
 struct MgObsSpec {
@@ -54,4 +57,6 @@ void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int 
 void mg_launch_clear_fresh(const MgDeviceState &S, cudaStream_t st);
 /* stand-alone render of one view: full_res ? [B,384,384,3] : [B,96,96,3] */
 void mg_launch_render_out(const MgDeviceState &S, int view, int full_res, uint8_t *out, cudaStream_t st);
+/* perm <- the envs ordered by the number of cached contacts (ascending), one launch */
+void mg_launch_order(const MgDeviceState &S, int *perm, cudaStream_t st);
 void mg_launch_state_gather(const MgDeviceState &S, const int32_t *env_ids_dev, int n, double *dblobs, int *iblobs, int scatter, cudaStream_t st);

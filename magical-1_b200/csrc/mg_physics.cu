@@ -1442,7 +1442,7 @@ __host__ __device__ inline int phys_smem_doubles(int max_blocks)
     return ((n + 15) & ~15) + 1;
 }
 
-template <int PHYS_THREADS_T, bool BLOCK_REG>
+template <int PHYS_THREADS_T, bool BLOCK_REG, bool PERM>
 __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
                                                                 uint8_t *done_out, float *score_out, int max_blocks)
 {
@@ -1462,11 +1462,11 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     const int lane = threadIdx.x & 31;
     const int grp = threadIdx.x / PHYS_LANES, gl = threadIdx.x % PHYS_LANES;
     const unsigned gmask = (unsigned)((1ull << PHYS_LANES) - 1) << (lane / PHYS_LANES * PHYS_LANES);
-    const int env0 = blockIdx.x * ENVS;
-    const int env = env0 + grp;
-    const bool active = env < S.num_envs;       /* idle groups of the last CTA still meet the barriers */
+    const int env0 = blockIdx.x * ENVS;         /* work slots env0 .. env0 + ENVS - 1 of this launch */
+    const bool active = env0 + grp < S.num_envs;   /* idle groups of the last CTA still meet the barriers */
+    const int env = PERM ? S.perm[active ? env0 + grp : env0] : (active ? env0 + grp : env0);
     const MgTables *T = (const MgTables *)phys_smem_raw;   /* only the fields before dl_off are valid */
-    const EnvRef g = env_ref(S.dstate, S.istate, active ? env : env0);
+    const EnvRef g = env_ref(S.dstate, S.istate, env);
     PhysSmemFixed *W = &sm[grp];
     __syncthreads();
     double *Wd = smd + (size_t)grp * nd;
@@ -1488,7 +1488,7 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     const bool solver = threadIdx.x < ENVS && env0 + lane < S.num_envs;
     EnvRef es = e;
     if (solver) {
-        const EnvRef gs = env_ref(S.dstate, S.istate, env0 + lane);
+        const EnvRef gs = env_ref(S.dstate, S.istate, PERM ? S.perm[env0 + lane] : env0 + lane);
         es.d = smd + (size_t)lane * nd; es.dc = es.d + con_off; es.i = sm[lane].i; es.da = gs.da; es.ia = gs.ia;
     }
 #endif
@@ -1609,6 +1609,41 @@ __global__ void mg_state_copy_kernel(MgDeviceState S, const int32_t *env_ids, in
     }
 }
 
+/* perm <- envs sorted by min(cached arbiters, 3), ascending and stable: envs without contacts first.  One CTA: every
+ * thread owns a contiguous run of envs, counts its four classes, and block-wide exclusive scans place them. */
+__global__ void __launch_bounds__(1024) mg_order_kernel(MgDeviceState S, int *perm)
+{
+    __shared__ int warp_sum[32];
+    __shared__ int class_base[5];
+    const int B = S.num_envs, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int per = (B + 1023) / 1024, e0 = t * per, e1 = min(B, e0 + per);
+    int cnt[4] = { 0, 0, 0, 0 };
+    for (int env = e0; env < e1; env++) cnt[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++;
+    int pos[4];
+    if (t == 0) class_base[0] = 0;
+    for (int c = 0; c < 4; c++) {
+        int v = cnt[c], incl = v;
+        for (int off = 1; off < 32; off <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += o; }
+        if (lane == 31) warp_sum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_sum[lane], wi = w;
+            for (int off = 1; off < 32; off <<= 1) { int o = __shfl_up_sync(0xffffffffu, wi, off); if (lane >= off) wi += o; }
+            warp_sum[lane] = wi - w;
+            if (lane == 31) class_base[c + 1] = class_base[c] + wi;
+        }
+        __syncthreads();
+        pos[c] = class_base[c] + warp_sum[warp] + incl - v;
+        __syncthreads();
+    }
+    for (int env = e0; env < e1; env++) perm[pos[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++] = env;
+}
+
+void mg_launch_order(const MgDeviceState &S, int *perm, cudaStream_t st)
+{
+    mg_order_kernel<<<1, 1024, 0, st>>>(S, perm);
+}
+
 void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st)
 {
     if (n <= 0) return;
@@ -1628,17 +1663,30 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
     const size_t smem = PHYS_TABLE_BYTES + per_env * envs;
     const size_t smem_full = PHYS_TABLE_BYTES + per_env * PHYS_ENVS;
     if (smem_full > attr_set) {
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
+        const int a = (int)smem_full;
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
         attr_set = smem_full;
     }
     const int grid = (S.num_envs + envs - 1) / envs;
     /* scenes with several blocks run the blocks' floor-friction pairs through the register formulas; with at most one
-     * block the generic constraint path measured faster (0.476 vs 0.502 ms at 4096 MoveToCorner envs) */
-    if (!wide) mg_physics_kernel<PHYS_THREADS / 2, true><<<grid, PHYS_THREADS / 2, smem, st>>>(S, actions, reward, done, score, max_blocks);
-    else if (max_blocks > 1) mg_physics_kernel<PHYS_THREADS, true><<<grid, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks);
-    else mg_physics_kernel<PHYS_THREADS, false><<<grid, PHYS_THREADS, smem, st>>>(S, actions, reward, done, score, max_blocks);
+     * block the generic constraint path measured faster (0.476 vs 0.502 ms at 4096 MoveToCorner envs).  The PERM
+     * instantiations take their envs through S.perm (mg_step in parts). */
+#define PHYS_LAUNCH(T_, R_, P_) mg_physics_kernel<T_, R_, P_><<<grid, T_, smem, st>>>(S, actions, reward, done, score, max_blocks)
+    if (S.perm) {
+        if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, true);
+        else if (max_blocks > 1) PHYS_LAUNCH(PHYS_THREADS, true, true);
+        else PHYS_LAUNCH(PHYS_THREADS, false, true);
+    } else {
+        if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, false);
+        else if (max_blocks > 1) PHYS_LAUNCH(PHYS_THREADS, true, false);
+        else PHYS_LAUNCH(PHYS_THREADS, false, false);
+    }
+#undef PHYS_LAUNCH
 }
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st)
 {

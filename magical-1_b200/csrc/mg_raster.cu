@@ -457,8 +457,9 @@ __global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int v
 {
     const MgTables *T = S.tables;
     const int lane = threadIdx.x & 31;
-    const int env = env_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (env >= env_end) return;
+    const int slot = env_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (slot >= env_end) return;
+    const int env = S.perm ? S.perm[slot] : slot;
     const double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
     const double *rp = pose + MG_BODY_ROBOT * MG_POSE_NF;
     const aff cam = view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
@@ -556,6 +557,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
     int env = A.env_begin + (int)(item / N_BANDS), band = (int)(item % N_BANDS);
     if (env >= A.env_end) return;
+    if (S.perm) env = S.perm[env];
     WarpSmem *W = (WarpSmem *)smem_raw + warp;
     const int y0 = band * BAND_ROWS;
 
