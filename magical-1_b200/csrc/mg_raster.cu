@@ -810,10 +810,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                 uint32_t o[4];
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    int w = half * 4 + k, px = w / 3, part = w % 3;   /* word w of the 12 output words */
-                    uint32_t t0 = rgb_of(src[part][0], src[part][1], src[part][2], px);
-                    uint32_t t1 = rgb_of(src[part + 1][0], src[part + 1][1], src[part + 1][2], px);
-                    o[k] = part == 0 ? (t0 | (t1 << 24)) : (part == 1 ? ((t0 >> 8) | (t1 << 16)) : ((t0 >> 16) | (t1 << 8)));
+                    /* word w of the 12 output words = bytes of frames `part` and `part + 1` at pixel px; win(g) is the
+                     * 32-bit window of frame g that starts at the pixel's first byte (one funnel shift), and one byte
+                     * permute picks r g b | r, g b | r g, b | r g b out of two windows */
+                    const int w = half * 4 + k, px = w / 3, part = w % 3;
+                    const int lo_w = (3 * px) >> 2, sh = 8 * ((3 * px) & 3);
+                    const uint32_t wa = sh ? __funnelshift_r(src[part][lo_w], src[part][lo_w < 2 ? lo_w + 1 : 2], sh) : src[part][lo_w];
+                    const uint32_t wb = sh ? __funnelshift_r(src[part + 1][lo_w], src[part + 1][lo_w < 2 ? lo_w + 1 : 2], sh) : src[part + 1][lo_w];
+                    o[k] = __byte_perm(wa, wb, part == 0 ? 0x4210 : (part == 1 ? 0x5421 : 0x6542));
                 }
                 dst[half] = make_uint4(o[0], o[1], o[2], o[3]);
             }
