@@ -425,17 +425,6 @@ __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, 
     return out;
 }
 
-/* bytes 3p .. 3p+2 of the 12-byte group (s0, s1, s2): the RGB of pixel p of four consecutive pixels */
-__device__ __forceinline__ uint32_t rgb_of(uint32_t s0, uint32_t s1, uint32_t s2, int p)
-{
-    switch (p) {
-    case 0: return s0 & 0xffffffu;
-    case 1: return __funnelshift_r(s0, s1, 24) & 0xffffffu;
-    case 2: return __funnelshift_r(s1, s2, 16) & 0xffffffu;
-    default: return s2 >> 8;
-    }
-}
-
 struct RenderArgs {
     int view;
     int mode;            /* 0: push into the frame ring (+ optional fused stack); 1: lo-res out; 2: full-res out */
