@@ -199,7 +199,9 @@ __device__ __forceinline__ int width_offset(int copy) { return copy == 0 ? 0 : (
  * lanes), the short ones are drawn by their own lanes side by side.  All copies of one outline carry the same
  * colour, so the order in which their pixels land does not matter.  The only copy of the line code in the kernel
  * (the kernel is bound by instruction fetch). */
+#ifndef LONG_LINE
 #define LONG_LINE 12
+#endif
 __device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool has, int x1, int y1, int x2, int y2, uint8_t c)
 {
     Line L = { 0, 0, 1, 1, 1, 1, 0, true, 1.0f };      /* len 0: nothing to draw */
