@@ -83,7 +83,9 @@ const char *mg_last_error(const mg_handle *h); /* h may be NULL: error of the la
 
 /* Reset `n` envs to host-sampled scenes.  env_ids_host == NULL means envs 0..n-1.
  * The frame stacks of those envs are refilled with the first rendered frame on the next
- * mg_step / mg_reset_obs (FlattenFrameStack.reset, benchmarks/__init__.py:139-147). */
+ * mg_step / mg_reset_obs (FlattenFrameStack.reset, benchmarks/__init__.py:139-147).
+ * The host arrays are copied before the call returns (they may be pageable and reused at once); the upload and the
+ * initialisation kernel run on `stream` without draining it. */
 int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream);
 
 /* Render the current state of every env into the frame stacks and write the stacked

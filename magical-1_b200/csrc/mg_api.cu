@@ -26,6 +26,12 @@ struct mg_handle {
     int max_blocks;          /* largest n_blocks ever installed: sizes the step kernel's shared memory */
     mg_scene *scene_stage_dev;  /* [B] staging for mg_set_scenes */
     int32_t *ids_stage_dev;     /* [B] */
+    /* pinned host side of the staging, two slots: mg_set_scenes copies the caller's (possibly pageable) arrays here and
+     * returns without draining the stream; a slot is reused once the init kernel that read it has run */
+    mg_scene *scene_stage_host[2];
+    int32_t *ids_stage_host[2];
+    cudaEvent_t stage_ev[2];
+    int stage_used[2], stage_slot;
     /* mg_step_host staging */
     int32_t *actions_dev;
     uint8_t *obs_dev;
@@ -122,6 +128,13 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     h->S.num_envs = B;
     CK(h, cudaMalloc(&h->scene_stage_dev, (size_t)B * sizeof(mg_scene)));
     CK(h, cudaMalloc(&h->ids_stage_dev, (size_t)B * sizeof(int32_t)));
+    for (int k = 0; k < 2; k++) {
+        CK(h, cudaMallocHost(&h->scene_stage_host[k], (size_t)B * sizeof(mg_scene)));
+        CK(h, cudaMallocHost(&h->ids_stage_host[k], (size_t)B * sizeof(int32_t)));
+        CK(h, cudaEventCreateWithFlags(&h->stage_ev[k], cudaEventDisableTiming));
+        h->stage_used[k] = 0;
+    }
+    h->stage_slot = 0;
     h->obs_bytes = (size_t)B * MG_LORES * MG_LORES * 3 * (cfg->n_groups > 0 ? cfg->n_groups : 1);
     CK(h, cudaMalloc(&h->actions_dev, (size_t)B * sizeof(int32_t)));
     CK(h, cudaMalloc(&h->obs_dev, h->obs_bytes));
@@ -164,6 +177,7 @@ extern "C" int mg_destroy(mg_handle *h)
     for (int c = 0; c < MG_HOST_CHUNKS; c++) cudaEventDestroy(h->chunk_done[c]);
     for (int c = 0; c < MG_STEP_PARTS; c++) { cudaStreamDestroy(h->part_stream[c]); cudaEventDestroy(h->part_done[c]); }
     cudaEventDestroy(h->fork_ev);
+    for (int k = 0; k < 2; k++) { cudaFreeHost(h->scene_stage_host[k]); cudaFreeHost(h->ids_stage_host[k]); cudaEventDestroy(h->stage_ev[k]); }
     cudaFree(h->perm_dev);
     for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (auto e : h->free_events) cudaEventDestroy(e);
@@ -193,12 +207,18 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
             return fail(h, MG_ERR_ARG, "mg_set_scenes: scene out of range");
     }
     for (int i = 0; i < n; i++) h->max_blocks = scenes_host[i].n_blocks > h->max_blocks ? scenes_host[i].n_blocks : h->max_blocks;
-    CK(h, cudaMemcpyAsync(h->scene_stage_dev, scenes_host, (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
-    if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, env_ids_host, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    const int slot = h->stage_slot ^= 1;
+    if (h->stage_used[slot]) CK(h, cudaEventSynchronize(h->stage_ev[slot]));          /* long done: two calls ago */
+    memcpy(h->scene_stage_host[slot], scenes_host, (size_t)n * sizeof(mg_scene));
+    if (env_ids_host) memcpy(h->ids_stage_host[slot], env_ids_host, (size_t)n * sizeof(int32_t));
+    /* the device side of the staging is one buffer: order this call behind the init kernel of the previous one */
+    if (h->stage_used[slot ^ 1]) CK(h, cudaStreamWaitEvent(st, h->stage_ev[slot ^ 1], 0));
+    CK(h, cudaMemcpyAsync(h->scene_stage_dev, h->scene_stage_host[slot], (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
+    if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, h->ids_stage_host[slot], (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     mg_launch_init(h->S, h->scene_stage_dev, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
     h->launches++;
-    /* the staging buffers are reused by the next call and the host arrays may be pageable */
-    CK(h, cudaStreamSynchronize(st));
+    CK(h, cudaEventRecord(h->stage_ev[slot], st));
+    h->stage_used[slot] = 1;
     return check_launch(h, "mg_init_kernel");
 }
 
