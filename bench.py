@@ -33,7 +33,7 @@ ENVS_PER_GPU = 4096
 OBS_BYTES_PER_ENV = 96 * 96 * 12       # algorithmic bytes written per env-step
 # dram__bytes_read.sum + dram__bytes_write.sum of one mg_render_kernel launch at 4096 envs (ncu --set full,
 # profiles/r1_ncu_summary.txt): 361.9 MB + 546.3 MB; per env it does not depend on the batch size
-NCU_DRAM_BYTES_PER_ENV = (359.571e6 + 567.884e6) / 4096
+NCU_DRAM_BYTES_PER_ENV = (359.468e6 + 513.831e6) / 4096
 NCU_TRAFFIC_SOURCE = 'profiles/r1e_ncu_summary.txt (ncu --set full, one launch, 4096 envs), scaled per env'
 METRIC = 'env_steps_per_sec_lores4e'
 UNIT = 'env-steps/s'
