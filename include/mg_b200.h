@@ -22,6 +22,8 @@
  *   mg_debug_reward           debug_shaped_reward()                  move_to_corner.py:86-100, pick_and_place.py:114-124
  *   mg_get_bodies             body.position/.angle/.velocity reads   magical/base_env.py:358-413 (debug_print_entity_spec)
  *   mg_get_state/mg_set_state (no reference equivalent: EzPickle re-constructs, base_env.py:20-46)
+ *   mg_get_status             (no reference equivalent: Chipmunk grows its arbiter hash without bound and lets
+ *                             NaNs propagate; this library's fixed capacities and its NaN guard report here)
  *   mg_frames_downsample      ResizeDictObservation on stored frames magical/benchmarks/__init__.py:150-190
  *   mg_frames_stack           FlattenFrameStack / EagerDictFrameStack / ChannelsFirst replayed over a stored
  *                             trajectory (preprocess_demos_with_wrapper) magical/saved_trajectories.py:87-149
@@ -124,6 +126,16 @@ int mg_debug_reward(mg_handle *h, float *reward_dev, void *stream);
  * scene order; unused slots are zero.  out_host: double [B][MG_MAX_BODIES][6] = x,y,angle,vx,vy,w.
  * Synchronous. */
 int mg_get_bodies(mg_handle *h, double *out_host);
+
+/* Per-env health flags raised by mg_step* since mg_create or the last call with clear != 0 (sticky across
+ * resets).  status_host: int32 [B].  Synchronous (drains the device).
+ *   MG_STATUS_ARB_OVERFLOW  a sub-step found more simultaneous cached contacts (live + up to 3 stamps old) than
+ *                           the per-env cache holds (160 shape pairs); the extra contact was dropped, so the env
+ *                           no longer follows the reference
+ *   MG_STATUS_NONFINITE     a body position / angle / velocity became NaN or Inf */
+#define MG_STATUS_ARB_OVERFLOW 1
+#define MG_STATUS_NONFINITE 2
+int mg_get_status(mg_handle *h, int32_t *status_host, int clear);
 
 /* Opaque per-env checkpoint blobs (bodies, cached impulses, contact cache, counters). */
 size_t mg_state_size(const mg_handle *h);

@@ -64,6 +64,7 @@ class ResetSpec(C.Structure):
 
 
 ERR_PLACEMENT = -4
+STATUS_ARB_OVERFLOW, STATUS_NONFINITE = 1, 2      # mg_get_status bits
 
 # every symbol include/mg_b200.h declares: name -> (restype, argtypes)
 _VP = C.c_void_p
@@ -81,6 +82,7 @@ SYMBOLS = {
     'mg_score': (C.c_int, [_VP, _VP, _VP]),
     'mg_debug_reward': (C.c_int, [_VP, _VP, _VP]),
     'mg_get_bodies': (C.c_int, [_VP, _VP]),
+    'mg_get_status': (C.c_int, [_VP, _VP, C.c_int]),
     'mg_state_size': (C.c_size_t, [_VP]),
     'mg_get_state': (C.c_int, [_VP, _VP, C.c_int, _VP]),
     'mg_set_state': (C.c_int, [_VP, _VP, C.c_int, _VP]),

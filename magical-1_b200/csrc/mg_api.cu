@@ -45,6 +45,10 @@ struct mg_handle {
     int step_order;                          /* group the envs of a part by contact load (mg_order_kernel) */
     int *perm_dev;                           /* [B] env order of the current mg_step */
     cudaEvent_t chunk_done[MG_HOST_CHUNKS];
+    /* last work this handle put on a CALLER's stream (mg_set_scenes, mg_reset_obs, mg_step*, mg_render): mg_step_host
+     * runs on own_stream and must not start before it (the caller need not synchronise between the two) */
+    cudaEvent_t caller_ev;
+    int caller_ev_used;
     /* accounting */
     int64_t launches;
     int timing;
@@ -113,6 +117,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaMalloc(&h->S.prims, (size_t)B * MG_MAX_PRIMS * sizeof(MgPrim)));
     CK(h, cudaMalloc(&h->S.n_prims, (size_t)B * sizeof(int)));
     CK(h, cudaMemset(h->S.n_prims, 0, (size_t)B * sizeof(int)));
+    CK(h, cudaMalloc(&h->S.status, (size_t)B * sizeof(int)));
+    CK(h, cudaMemset(h->S.status, 0, (size_t)B * sizeof(int)));
     CK(h, cudaMalloc(&h->S.poses, (size_t)B * MG_POSE_STRIDE * sizeof(double)));
     CK(h, cudaMemset(h->S.poses, 0, (size_t)B * MG_POSE_STRIDE * sizeof(double)));
     for (int v = 0; v < 2; v++) {
@@ -149,6 +155,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
         CK(h, cudaEventCreateWithFlags(&h->part_done[c], cudaEventDisableTiming));
     }
     CK(h, cudaEventCreateWithFlags(&h->fork_ev, cudaEventDisableTiming));
+    CK(h, cudaEventCreateWithFlags(&h->caller_ev, cudaEventDisableTiming));
+    h->caller_ev_used = 0;
     {
         /* 16 parts of >= 256 envs measured best at 4096 envs (0.94 -> 0.87 ms); MG_STEP_PARTS=1 keeps the plain sequence */
         const char *ev = getenv("MG_STEP_PARTS");
@@ -169,20 +177,27 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     cudaFree(h->S.dstate); cudaFree(h->S.istate); cudaFree(h->S.scenes); cudaFree(h->S.prims);
-    cudaFree(h->S.n_prims); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
+    cudaFree(h->S.n_prims); cudaFree(h->S.status); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
     for (int v = 0; v < 2; v++) { cudaFree(h->S.sprims[v]); cudaFree(h->S.sverts[v]); cudaFree(h->S.dashv[v]); }
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
     cudaStreamDestroy(h->own_stream); cudaStreamDestroy(h->copy_stream);
     for (int c = 0; c < MG_HOST_CHUNKS; c++) cudaEventDestroy(h->chunk_done[c]);
     for (int c = 0; c < MG_STEP_PARTS; c++) { cudaStreamDestroy(h->part_stream[c]); cudaEventDestroy(h->part_done[c]); }
-    cudaEventDestroy(h->fork_ev);
+    cudaEventDestroy(h->fork_ev); cudaEventDestroy(h->caller_ev);
     for (int k = 0; k < 2; k++) { cudaFreeHost(h->scene_stage_host[k]); cudaFreeHost(h->ids_stage_host[k]); cudaEventDestroy(h->stage_ev[k]); }
     cudaFree(h->perm_dev);
     for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (auto e : h->free_events) cudaEventDestroy(e);
     delete h;
     return MG_OK;
+}
+
+/* remember the tail of the work just put on a caller's stream so that mg_step_host (own_stream) can order itself behind it */
+static void mark_caller(mg_handle *h, cudaStream_t st)
+{
+    if (st == h->own_stream) return;
+    if (cudaEventRecord(h->caller_ev, st) == cudaSuccess) h->caller_ev_used = 1;
 }
 
 static int check_launch(mg_handle *h, const char *what)
@@ -219,6 +234,7 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
     h->launches++;
     CK(h, cudaEventRecord(h->stage_ev[slot], st));
     h->stage_used[slot] = 1;
+    mark_caller(h, st);
     return check_launch(h, "mg_init_kernel");
 }
 
@@ -254,6 +270,7 @@ extern "C" int mg_step_physics(mg_handle *h, const int32_t *actions_dev, float *
     mg_launch_physics(h->S, actions_dev, reward_dev, done_dev, score_dev, h->max_blocks, st);
     h->launches++;
     time_end(h, 0, 1, st);
+    mark_caller(h, st);
     return check_launch(h, "mg_physics_kernel");
 }
 
@@ -278,6 +295,7 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
     if (!h->fused && obs_dev && h->spec.n_groups > 0) { mg_launch_compose(h->S, h->spec, h->slots, obs_dev, st); nl++; }
     mg_launch_clear_fresh(h->S, st); nl++;
     h->launches += nl;
+    mark_caller(h, st);
     return check_launch(h, "mg_render_kernel");
 }
 
@@ -325,6 +343,7 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
     }
     mg_launch_clear_fresh(h->S, st);
     h->launches += 3 * P + 1 + (ordered ? 1 : 0);
+    mark_caller(h, st);
     return check_launch(h, "mg_step (parts)");
 }
 
@@ -345,6 +364,8 @@ extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *
     const int B = h->cfg.num_envs;
     cudaStream_t st = h->own_stream;
     CK(h, cudaSetDevice(h->cfg.device));
+    /* resets / renders the caller queued on its own stream (mg_set_scenes, mg_reset_obs, mg_step*) come first */
+    if (h->caller_ev_used) { CK(h, cudaStreamWaitEvent(st, h->caller_ev, 0)); h->caller_ev_used = 0; }
     CK(h, cudaMemcpyAsync(h->actions_dev, actions_host, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     int rc = mg_step_physics(h, h->actions_dev, h->reward_dev, h->done_dev, h->score_dev, st);
     if (rc != MG_OK) return rc;
@@ -421,6 +442,16 @@ extern "C" int mg_get_bodies(mg_handle *h, double *out_host)
         for (int b = 0; b < MG_MAX_BODIES; b++)
             for (int k = 0; k < 6; k++)
                 out_host[((size_t)e * MG_MAX_BODIES + b) * 6 + k] = poses[(size_t)e * MG_POSE_STRIDE + (b + 1) * MG_POSE_NF + k];
+    return MG_OK;
+}
+
+extern "C" int mg_get_status(mg_handle *h, int32_t *status_host, int clear)
+{
+    if (!h || !status_host) return fail(h, MG_ERR_ARG, "mg_get_status: bad argument");
+    CK(h, cudaSetDevice(h->cfg.device));
+    CK(h, cudaDeviceSynchronize());
+    CK(h, cudaMemcpy(status_host, h->S.status, (size_t)h->cfg.num_envs * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    if (clear) CK(h, cudaMemset(h->S.status, 0, (size_t)h->cfg.num_envs * sizeof(int)));
     return MG_OK;
 }
 

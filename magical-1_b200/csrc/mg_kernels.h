@@ -29,7 +29,9 @@ struct MgDeviceState {
     /* optional order of the envs for this launch (NULL = identity): the step and render kernels take env perm[k] for
      * their k-th work slot, so that a part of the batch can be any set of envs (mg_step groups envs by contact load) */
     const int *perm;
+    int *status;             /* [B] sticky MG_STATUS_* bits (NULL: not collected) */
 };
+#define MG_MAX_DEVICES 64    /* CUDA ordinals the per-device launch attributes are tracked for */
 
 struct MgObsSpec {
     int n_groups;

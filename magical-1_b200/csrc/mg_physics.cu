@@ -22,6 +22,7 @@
 #include <stdlib.h>
 #include <stddef.h>
 #include <stdio.h>
+#include <mutex>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
@@ -501,7 +502,7 @@ __device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Ma
     uint32_t old_hash[2] = { 0, 0 };
     double old_jn[2] = { 0, 0 }, old_jt[2] = { 0, 0 };
     if (slot < 0) {
-        if (n_arbs >= MG_NARB) return -1;
+        if (n_arbs >= MG_NARB) { IF(e, I_STATUS) = IF(e, I_STATUS) | MG_STATUS_ARB_OVERFLOW; return -1; }   /* flagged, never silent */
         slot = n_arbs;
         IF(e, I_NARBS) = n_arbs + 1;
     } else {
@@ -1560,18 +1561,23 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     for (int f = gl; f < nc * C_NF; f += PHYS_LANES) g.dc[f] = Wd[con_off + f];
     /* pose export for the rasteriser and mg_get_bodies: lane = body */
     double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
+    bool finite = true;      /* a NaN / Inf body state is flagged per env, never propagated silently */
     for (int b = gl; b < MG_NB; b += PHYS_LANES) {
         double *o = pose + b * MG_POSE_NF;
         if (b < nb) {
             o[0] = BF(e, b, B_PX); o[1] = BF(e, b, B_PY); o[2] = BF(e, b, B_A);
             o[3] = BF(e, b, B_VX); o[4] = BF(e, b, B_VY); o[5] = BF(e, b, B_W);
             o[6] = BF(e, b, B_RX); o[7] = BF(e, b, B_RY);
+            finite = finite && isfinite(o[0]) && isfinite(o[1]) && isfinite(o[2]) && isfinite(o[3]) && isfinite(o[4]) && isfinite(o[5]);
         } else {
             for (int k = 0; k < MG_POSE_NF; k++) o[k] = 0.0;
         }
     }
+    const bool any_bad = __ballot_sync(gmask, !finite) != 0;
     __syncwarp(gmask);
     if (gl == 0) {
+        const int status = IF(e, I_STATUS) | (any_bad ? MG_STATUS_NONFINITE : 0);
+        if (status) { g.i[I_STATUS] = status; if (S.status) S.status[env] |= status; }
         /* scores read goals / targets too: use the HBM copy just written */
         double rew = 0.0, eval_score = 0.0;
         if (done) rew = eval_score = env_score(g, T);
@@ -1651,7 +1657,13 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
 }
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st)
 {
-    static size_t attr_set = 0;
+    /* the shared-memory opt-in is a per-device (per-context) function attribute: track it per CUDA ordinal */
+    static size_t attr_set_dev[MG_MAX_DEVICES] = { 0 };
+    static std::mutex attr_mu;
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    std::lock_guard<std::mutex> attr_lock(attr_mu);
+    size_t &attr_set = attr_set_dev[dev_ < 0 || dev_ >= MG_MAX_DEVICES ? 0 : dev_];
     if (max_blocks < 0) max_blocks = 0;
     if (max_blocks > MG_MAX_BLOCKS) max_blocks = MG_MAX_BLOCKS;
     /* 16 envs per CTA while two such CTAs fit one SM; larger scenes run 8 envs per CTA so that three (two

@@ -20,6 +20,7 @@
  * of an integer DDA line after Cohen-Sutherland clipping with a float slope.
  */
 #include <cuda_runtime.h>
+#include <mutex>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
@@ -869,7 +870,13 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
 {
     if (A.env_end <= A.env_begin) return;
     mg_launch_geometry(S, A.view, A.env_begin, A.env_end, st);
-    static bool attr_set = false;
+    /* per-device function attribute (see mg_launch_physics) */
+    static bool attr_set_dev[MG_MAX_DEVICES] = { false };
+    static std::mutex attr_mu;
+    int dev_ = 0;
+    cudaGetDevice(&dev_);
+    std::lock_guard<std::mutex> attr_lock(attr_mu);
+    bool &attr_set = attr_set_dev[dev_ < 0 || dev_ >= MG_MAX_DEVICES ? 0 : dev_];
     size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA;
     if (!attr_set) {
         cudaFuncSetAttribute(mg_render_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

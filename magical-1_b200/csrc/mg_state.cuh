@@ -20,7 +20,8 @@
 #define MG_BODY_BLOCK0 (1 + MG_RB_COUNT)
 #define MG_NCON 32                      /* 10 robot constraints + 2 per block */
 #define MG_NSHAPE (4 + 5 + MG_MAX_BLOCKS * MG_STAR_PIECES)
-#define MG_NARB 64                      /* cached arbiters (live + up to 3 stamps old) */
+#define MG_NARB 160                     /* cached arbiters (live + up to 3 stamps old); the oracle holds the same number
+                                         * (oracle/orc.h ORC_MAX_ARBS) so that both overflow, and flag it, at the same point */
 
 /* ---- double fields ---- */
 enum { B_PX, B_PY, B_A, B_VX, B_VY, B_W, B_VBX, B_VBY, B_WB, B_RX, B_RY, B_MINV, B_IINV, B_NF };
@@ -57,6 +58,7 @@ enum {
     I_NCON, I_NSHAPES, I_NARBS,
     I_STAMP, I_STEPPED /* 0 until the first space step (Chipmunk prev_dt == 0) */, I_EPISODE_STEPS,
     I_FRESH,        /* frame stacks must be refilled with the next rendered frame */
+    I_STATUS,       /* MG_STATUS_* bits raised since the last reset (copied into MgDeviceState::status, which is sticky) */
     I_BLOCK0,       /* per block: type | colour << 8 | role << 16 */
     I_GOAL0 = I_BLOCK0 + MG_MAX_BLOCKS,   /* per goal: colour | (want_block + 1) << 8 */
     I_CON0 = I_GOAL0 + MG_MAX_GOALS,      /* per constraint: kind | a << 8 | b << 16 */

@@ -262,15 +262,14 @@ class BatchedMagicalEnv:
             self._check(self._lib.mg_step(self._h, L.ptr(actions), L.ptr(self._obs), L.ptr(self._reward), L.ptr(self._done),
                                           L.ptr(self._score), st))
             self._episode_steps += 1
-            return self._make_obs(), self._reward, self._done.bool(), {'eval_score': self._score}
+            # clones on every path: the internal buffers are overwritten by the next step (B floats, negligible)
+            return self._make_obs(), self._reward.clone(), self._done.bool(), {'eval_score': self._score.clone()}
         self._check(self._lib.mg_step_physics(self._h, L.ptr(actions), L.ptr(self._reward), L.ptr(self._done),
                                               L.ptr(self._score), st))
         self._episode_steps += 1
         finished = np.nonzero(self._episode_steps >= self._horizons)[0]
-        reward, done, score = self._reward, self._done.bool(), self._score
+        reward, done, score = self._reward.clone(), self._done.bool(), self._score.clone()
         if len(finished) and self.auto_reset:
-            # results of the finished episodes must survive the next step's writes
-            reward, score = reward.clone(), score.clone()
             self.set_scenes(finished, self._sample_many(finished))
         self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
         return self._make_obs(), reward, done, {'eval_score': score}
@@ -349,6 +348,13 @@ class BatchedMagicalEnv:
         torch = _torch()
         out = torch.empty(self.num_envs, dtype=torch.float32, device=self.device)
         self._check(self._lib.mg_debug_reward(self._h, L.ptr(out), self._stream()))
+        return out
+
+    def status(self, clear=False):
+        """int32 [B] of sticky health flags (_lib.STATUS_ARB_OVERFLOW: a contact was dropped because the per-env
+        arbiter cache was full; _lib.STATUS_NONFINITE: a body state became NaN / Inf).  Synchronous."""
+        out = np.zeros(self.num_envs, np.int32)
+        self._check(self._lib.mg_get_status(self._h, out.ctypes.data, int(bool(clear))))
         return out
 
     def get_state(self, env_ids=None):

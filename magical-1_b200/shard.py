@@ -32,21 +32,25 @@ def all_gather_scores(local_scores, num_envs, rank, world, global_index=None):
     sizes = [shard_range(num_envs, r, world)[1] - shard_range(num_envs, r, world)[0] for r in range(world)]
     n_max = max(sizes)
     dev = local_scores.device
-    send = torch.zeros(2, n_max, dtype=torch.float32, device=dev)
+    # one int32 buffer per rank: row 0 = the scores' f32 bit patterns, row 1 = global env indices (exact for any
+    # batch size; -1 = padding), so that ONE collective moves both
+    send = torch.full((2, n_max), -1, dtype=torch.int32, device=dev)
     n = local_scores.numel()
-    send[0, :n] = local_scores.to(torch.float32)
+    send[0, :n] = local_scores.to(torch.float32).contiguous().view(torch.int32)
     lo = shard_range(num_envs, rank, world)[0]
     gidx = torch.arange(lo, lo + n, device=dev) if global_index is None else torch.as_tensor(global_index, device=dev)
-    send[1, :n] = gidx.to(torch.float32)
+    send[1, :n] = gidx.to(torch.int32)
     if world > 1 and dist.is_initialized():
         # flat buffers: the same call works for NCCL (CUDA tensors) and gloo (CPU tensors)
-        recv = torch.zeros(world * 2 * n_max, dtype=torch.float32, device=dev)
+        recv = torch.empty(world * 2 * n_max, dtype=torch.int32, device=dev)
         dist.all_gather_into_tensor(recv, send.reshape(-1))
         recv = recv.reshape(world, 2, n_max)
     else:
         recv = send[None]
+    # one scatter for all ranks: padding entries (index -1) are masked out
+    idx = recv[:, 1, :].reshape(-1).long()
+    val = recv[:, 0, :].reshape(-1).contiguous().view(torch.float32)
+    keep = idx >= 0
     out = torch.zeros(num_envs, dtype=torch.float32, device=dev)
-    for r in range(recv.shape[0]):
-        k = sizes[r] if recv.shape[0] > 1 else n
-        out[recv[r, 1, :k].long()] = recv[r, 0, :k]
+    out[idx[keep]] = val[keep]
     return out
