@@ -142,6 +142,17 @@ size_t mg_state_size(const mg_handle *h);
 int mg_get_state(mg_handle *h, const int32_t *env_ids_host, int n, void *blobs_host);
 int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, const void *blobs_host);
 
+/* mg_get_state for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and byte-identical blobs as mg_get_state, but the device-side gather
+ * scratch is a fixed file-scope __device__ array (about 1.25 MB, held by every GPU that loads the library until
+ * exit) instead of a per-call cudaMalloc: the call issues no cudaMalloc / cudaFree / allocating library routine.
+ * At most MG_NOALLOC_MAX_ENVS envs per call; a larger n is rejected with MG_ERR_ARG and a message naming the limit
+ * (call it in slices).  All calls share the one scratch array: calls that overlap on the GPU (several host threads,
+ * or several handles on one device, at the same time) race on it -- serialise them.  Synchronous. */
+#define MG_NOALLOC_MAX_ENVS 32
+int mg_get_state_noalloc(mg_handle *h, const int32_t *env_ids_host, int n, void *blobs_host);
+
 /* Kernel launches issued through this handle so far (for bench.py's gpu_launches). */
 int64_t mg_launch_count(const mg_handle *h);
 /* CUDA-event time (ms) accumulated over the physics / render kernels since the last call

@@ -64,6 +64,7 @@ class ResetSpec(C.Structure):
 
 
 ERR_PLACEMENT = -4
+NOALLOC_MAX_ENVS = 32                              # mg_get_state_noalloc: envs per call
 STATUS_ARB_OVERFLOW, STATUS_NONFINITE = 1, 2      # mg_get_status bits
 
 # every symbol include/mg_b200.h declares: name -> (restype, argtypes)
@@ -86,6 +87,7 @@ SYMBOLS = {
     'mg_state_size': (C.c_size_t, [_VP]),
     'mg_get_state': (C.c_int, [_VP, _VP, C.c_int, _VP]),
     'mg_set_state': (C.c_int, [_VP, _VP, C.c_int, _VP]),
+    'mg_get_state_noalloc': (C.c_int, [_VP, _VP, C.c_int, _VP]),
     'mg_launch_count': (C.c_int64, [_VP]),
     'mg_set_timing': (C.c_int, [_VP, C.c_int]),
     'mg_kernel_ms': (C.c_double, [_VP, C.c_int, C.c_int, C.POINTER(C.c_int64)]),

@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "mg_kernels.h"
@@ -530,6 +531,103 @@ extern "C" int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, co
     /* restored envs may hold any number of blocks */
     if (h) h->max_blocks = MG_MAX_BLOCKS;
     return state_xfer(h, env_ids_host, n, (unsigned char *)blobs_host, true);
+}
+
+/* ------------------------------------------------------------------ mg_get_state_noalloc
+ * The checkpoint gather for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc): same blobs as mg_get_state, but the device-side gather scratch that state_xfer
+ * cudaMallocs per call lives in a file-scope __device__ array of fixed size instead, so this entry point calls no
+ * cudaMalloc / cudaFree / allocating library routine.  Every GPU that loads the library holds the array until exit.
+ * All calls share it: two calls that overlap on the GPU (two host threads, two handles on one device) race on it. */
+#define MG_NOALLOC_IDS_BYTES (((size_t)MG_NOALLOC_MAX_ENVS * sizeof(int32_t) + 255) & ~(size_t)255)
+#define MG_NOALLOC_D_BYTES ((size_t)MG_NOALLOC_MAX_ENVS * D_NF * sizeof(double))
+#define MG_NOALLOC_I_BYTES ((size_t)MG_NOALLOC_MAX_ENVS * I_NF * sizeof(int))
+#define MG_NOALLOC_BYTES (MG_NOALLOC_IDS_BYTES + MG_NOALLOC_D_BYTES + MG_NOALLOC_I_BYTES)
+/* [ env ids | MAX x D_NF doubles | MAX x I_NF ints ]  (about 1.25 MB for 32 envs) */
+static __device__ __align__(256) unsigned char mg_noalloc_scratch[MG_NOALLOC_BYTES];
+
+/* variant of mg_state_copy_kernel (gather direction) whose ids and blobs live in the scratch passed in */
+__global__ void mg_state_gather_noalloc_kernel(MgDeviceState S, int n, unsigned char *scratch)
+{
+    const int k = blockIdx.x;
+    if (k >= n) return;
+    const int32_t *ids = (const int32_t *)scratch;
+    double *dblobs = (double *)(scratch + MG_NOALLOC_IDS_BYTES);
+    int *iblobs = (int *)(scratch + MG_NOALLOC_IDS_BYTES + MG_NOALLOC_D_BYTES);
+    const int env = ids[k];
+    const double *d = S.dstate + mg_field_index(env, D_NF, 0);
+    const int *iv = S.istate + mg_field_index(env, I_NF, 0);
+    for (int f = threadIdx.x; f < D_NF; f += blockDim.x) dblobs[(size_t)k * D_NF + f] = d[(size_t)f * MG_GROUP];
+    for (int f = threadIdx.x; f < I_NF; f += blockDim.x) iblobs[(size_t)k * I_NF + f] = iv[(size_t)f * MG_GROUP];
+}
+
+/* device address of the scratch, looked up once per device with that device current: in host code the array's
+ * name is only a host-side stand-in for the symbol, never a device address */
+static int noalloc_scratch_ptr(mg_handle *h, unsigned char **out)
+{
+    static unsigned char *ptr_dev[MG_MAX_DEVICES] = { nullptr };
+    static std::mutex mu;
+    const int dev = h->cfg.device;
+    if (dev < 0 || dev >= MG_MAX_DEVICES) return fail(h, MG_ERR_ARG, "mg_get_state_noalloc: device ordinal beyond MG_MAX_DEVICES");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr_dev[dev]) {
+        void *p = nullptr;
+        CK(h, cudaGetSymbolAddress(&p, mg_noalloc_scratch));      /* cudaSetDevice(dev) was done by the caller */
+        ptr_dev[dev] = (unsigned char *)p;
+    }
+    *out = ptr_dev[dev];
+    return MG_OK;
+}
+
+extern "C" int mg_get_state_noalloc(mg_handle *h, const int32_t *env_ids_host, int n, void *blobs_host)
+{
+    if (!h || !blobs_host || n < 0) return fail(h, MG_ERR_ARG, "mg_get_state_noalloc: bad argument");
+    if (n > MG_NOALLOC_MAX_ENVS) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "mg_get_state_noalloc: n = %d exceeds MG_NOALLOC_MAX_ENVS = %d (fixed device scratch); "
+                                  "call it in slices or use mg_get_state", n, MG_NOALLOC_MAX_ENVS);
+        return fail(h, MG_ERR_ARG, msg);
+    }
+    if (n == 0) return MG_OK;
+    int32_t ids[MG_NOALLOC_MAX_ENVS];
+    for (int i = 0; i < n; i++) {
+        ids[i] = env_ids_host ? env_ids_host[i] : i;
+        if (ids[i] < 0 || ids[i] >= h->cfg.num_envs) return fail(h, MG_ERR_ARG, "mg_get_state_noalloc: env id out of range");
+    }
+    CK(h, cudaSetDevice(h->cfg.device));
+    unsigned char *scratch = nullptr;
+    int rc = noalloc_scratch_ptr(h, &scratch);
+    if (rc != MG_OK) return rc;
+    CK(h, cudaDeviceSynchronize());
+    /* nothing in the scratch has to start at zero: the ids and every blob word read back below are written by this
+     * call (ids by the copy, blobs by the kernel), whatever an earlier call left behind */
+    CK(h, cudaMemcpy(scratch, ids, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice));
+    mg_state_gather_noalloc_kernel<<<n, 128, 0, 0>>>(h->S, n, scratch);
+    h->launches++;
+    rc = check_launch(h, "mg_state_gather_noalloc_kernel");
+    if (rc != MG_OK) return rc;
+    CK(h, cudaDeviceSynchronize());
+    const size_t sz = mg_state_size(h);
+    const unsigned char *dblobs = scratch + MG_NOALLOC_IDS_BYTES, *iblobs = dblobs + MG_NOALLOC_D_BYTES;
+    for (int i = 0; i < n; i++) {
+        unsigned char *b = (unsigned char *)blobs_host + (size_t)i * sz;
+        const int e = ids[i];
+        CK(h, cudaMemcpy(b, dblobs + (size_t)i * BLOB_D, BLOB_D, cudaMemcpyDeviceToHost));
+        CK(h, cudaMemcpy(b + BLOB_D, iblobs + (size_t)i * BLOB_I, BLOB_I, cudaMemcpyDeviceToHost));
+        unsigned char *p = b + BLOB_D + BLOB_I;
+        CK(h, cudaMemcpy(p, h->S.scenes + e, BLOB_SCENE, cudaMemcpyDeviceToHost)); p += BLOB_SCENE;
+        CK(h, cudaMemcpy(p, h->S.prims + (size_t)e * MG_MAX_PRIMS, MG_MAX_PRIMS * sizeof(MgPrim), cudaMemcpyDeviceToHost)); p += MG_MAX_PRIMS * sizeof(MgPrim);
+        CK(h, cudaMemcpy(p, h->S.n_prims + e, sizeof(int), cudaMemcpyDeviceToHost));
+        memset(p + sizeof(int), 0, 8 - sizeof(int)); p += 8;
+        for (int v = 0; v < 2; v++)
+            for (int a = 0; a < MG_MAX_RING; a++) {
+                const int slot = (h->slots[v] - (MG_MAX_RING - 1 - a)) & (MG_MAX_RING - 1);
+                CK(h, cudaMemcpy(p, h->S.ring[v] + ((size_t)e * MG_MAX_RING + slot) * MG_FRAME_BYTES, MG_FRAME_BYTES, cudaMemcpyDeviceToHost));
+                p += MG_FRAME_BYTES;
+            }
+        memset(p, 0, (size_t)(b + sz - p));      /* tail padding of the blob */
+    }
+    return MG_OK;
 }
 
 extern "C" int64_t mg_launch_count(const mg_handle *h) { return h ? h->launches : 0; }
