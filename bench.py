@@ -1,14 +1,20 @@
-#!/usr/bin/env python
 """bench.py -- env-steps/sec of the MAGICAL hot path with 96x96 LoRes4E observations.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg1|cfg2|cfg3|cfg5] [--impl reference]
 
-Workload (BASELINE.json configs[1]): MoveToCorner-Demo-LoRes4E-v0, 4096 envs per GPU, scripted random
-actions, envs sharded by index across ranks with no data-path collective (weak scaling); one NCCL
-all-gather of episode scores when episodes end.  One "step" = one env-step of every env of the batch:
-action decode, 10 physics sub-steps, score at the horizon, ego render at 384^2, 4x area downsample, 4-frame
-stack.  Finished episodes are reset inside the timed region from initial states the native reset engine sampled
-on host threads while the previous episode was running (reference RNG, one RandomState stream per env).
+Workloads (BASELINE.json configs; the default, cfg1, is the one the metric is quoted on):
+  cfg1  MoveToCorner-Demo-LoRes4E-v0          4096 envs per GPU   (configs[1])
+  cfg2  FindDupe-TestLayout-LoRes4E-v0       16384 envs per GPU   (configs[2])
+  cfg3  ClusterColour-TestAll-LoRes4E-v0     32768 envs per GPU, block count forced to 10 (configs[3])
+  cfg5  the 60 benchmark ids (8 tasks x all variants) mixed, 4096 envs per GPU, sharded by env index over the
+        ranks (shard.shard_env_ids), per-step NCCL all-gather of the episode scores (configs[4])
+One "step" = one env-step of every env of the batch: action decode, 10 physics sub-steps, score at the horizon, ego
+render at 384^2, 4x area downsample, 4-frame stack.  Episodes are PHASED: env i starts its first episode i mod horizon
+steps late (an untimed pre-roll), so on EVERY step about B / horizon envs reach their horizon, report their score and
+start their next episode inside the step (mg_queue_resets: reset between the step's physics and its render, scenes
+sampled ahead by the reset feeder thread with the reference RNG) -- any timed window, the driver's 20 steps included,
+holds its proportional share of horizon steps.  With N > 1 ranks every step also all-gathers the ranks' eval scores over
+NCCL (asynchronously, double-buffered).
 
 --impl reference times the CPU oracle port (oracle/, the restated pymunk+pygame path; the reference itself
 cannot be imported here: pymunk/pygame/gym are not installed) on all host cores.
@@ -28,15 +34,32 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-ENV_ID = 'MoveToCorner-Demo-LoRes4E-v0'
-ENVS_PER_GPU = 4096
+WORKLOADS = {
+    'cfg1': dict(ids=['MoveToCorner-Demo-LoRes4E-v0'], envs=4096, label='BASELINE.json configs[1]'),
+    'cfg2': dict(ids=['FindDupe-TestLayout-LoRes4E-v0'], envs=16384, label='BASELINE.json configs[2]'),
+    'cfg3': dict(ids=['ClusterColour-TestAll-LoRes4E-v0'], envs=32768, force_blocks=10,
+                 label='BASELINE.json configs[3] (CountPlus, block count forced to the maximum, 10)'),
+    'cfg5': dict(ids='bench60', envs=4096, label='BASELINE.json configs[4]: 8 tasks x all variants (60 ids) mixed'),
+}
+BENCH_TASKS = ('MoveToCorner', 'MoveToRegion', 'MatchRegions', 'MakeLine', 'FindDupe', 'FixColour', 'ClusterColour', 'ClusterShape')
 OBS_BYTES_PER_ENV = 96 * 96 * 12       # algorithmic bytes written per env-step
-# dram__bytes_read.sum + dram__bytes_write.sum of one mg_render_kernel launch at 4096 envs (ncu --set full,
-# profiles/r1_ncu_summary.txt): 361.9 MB + 546.3 MB; per env it does not depend on the batch size
+# dram__bytes_read.sum + dram__bytes_write.sum of one mg_render_kernel launch at 4096 MoveToCorner envs (ncu --set full);
+# per env it does not depend on the batch size
 NCU_DRAM_BYTES_PER_ENV = (359.468e6 + 513.831e6) / 4096
-NCU_TRAFFIC_SOURCE = 'profiles/r1e_ncu_summary.txt (ncu --set full, one launch, 4096 envs), scaled per env'
+NCU_TRAFFIC_SOURCE = 'profiles/r1e_ncu_summary.txt (ncu --set full, one launch, 4096 MoveToCorner envs), scaled per env'
 METRIC = 'env_steps_per_sec_lores4e'
 UNIT = 'env-steps/s'
+SCENE_NBLOCKS_WORD = 2                  # int32 index of mg_scene.n_blocks (include/mg_scene.h)
+
+
+def workload_ids(m, wl):
+    """The registered ids of a workload (cfg5: the 60 base ids of the eight benchmark tasks, LoRes4E stacks)."""
+    if wl['ids'] != 'bench60':
+        return list(wl['ids'])
+    ids = [i for i in m.ALL_REGISTERED_ENVS
+           if m.spec(i)['preproc'] is None and i.split('-')[0] in BENCH_TASKS and 'DebugReward' not in i]
+    assert len(ids) == 60, len(ids)
+    return ids
 
 
 def host_cores():
@@ -46,23 +69,28 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def sample_pool(m, num_envs, n_episodes, seed0):
-    """Initial states for `n_episodes` consecutive episodes of every env: env i draws from its own
-    RandomState(seed0 + i), episode after episode, exactly as successive reset() calls would."""
+def sample_scenes(m, env_ids, seed0, force_blocks=None):
+    """One host-sampled initial state per entry of `env_ids` (entry i from RandomState(seed0 + i), re-drawn from the
+    same stream after a PlacementError / until the block count is `force_blocks`), packed as a ctypes array."""
     from magical_b200 import _lib as L
     from magical_b200 import tasks
-    sp = m.spec(ENV_ID)
-    kw = dict(sp['kwargs'])
-    rand_dynamics = kw.pop('rand_dynamics', False)
-    for k in ('res_hw', 'fps', 'phys_steps', 'phys_iter', 'max_episode_steps'):
-        kw.pop(k)
-    rngs = [np.random.RandomState(seed0 + i) for i in range(num_envs)]
-    pool = []
-    for _ in range(n_episodes):
-        scenes = [tasks.sample_scene(sp['entry_point'], rngs[i], sp['max_episode_steps'], rand_dynamics=rand_dynamics, **kw)
-                  for i in range(num_envs)]
-        pool.append(L.scenes_array(scenes))
-    return pool, sp['max_episode_steps']
+    scenes = []
+    for i, env_id in enumerate(env_ids):
+        sp = m.spec(env_id)
+        kw = dict(sp['kwargs'])
+        rand_dynamics = kw.pop('rand_dynamics', False)
+        for k in ('res_hw', 'fps', 'phys_steps', 'phys_iter', 'max_episode_steps'):
+            kw.pop(k)
+        rng = np.random.RandomState(seed0 + i)
+        while True:
+            try:
+                sc = tasks.sample_scene(sp['entry_point'], rng, sp['max_episode_steps'], rand_dynamics=rand_dynamics, **kw)
+            except tasks.PlacementError:
+                continue
+            if force_blocks is None or sc.n_blocks == force_blocks:
+                break
+        scenes.append(sc)
+    return L.scenes_array(scenes)
 
 
 class ClockSampler:
@@ -112,24 +140,26 @@ class ClockSampler:
                 'samples': len(sm), 'reasons': sorted(reasons)}
 
 
-def cpu_baseline(n_threads, seconds_target=12.0):
+def cpu_baseline(n_threads, wl_name, seconds_target=12.0):
     """The oracle port timed on the host cores on a bounded sample of the same workload (full reference
     step: 10 sub-steps, allo+ego 384^2 renders, three INTER_AREA resizes, score at the horizon)."""
     import magical_b200 as m
     from oracle import orc
     lib = orc.lib()
     m.register_envs()
-    n_envs = max(n_threads, 1) * 2
-    pool, horizon = sample_pool(m, n_envs, 1, 0)
+    wl = WORKLOADS[wl_name]
+    ids = workload_ids(m, wl)
+    n_envs = max(max(n_threads, 1) * 2, len(ids))
+    env_ids = [ids[i % len(ids)] for i in range(n_envs)]
+    packed = sample_scenes(m, env_ids, 0, wl.get('force_blocks'))
     scenes = (orc.Scene * n_envs)()
-    C.memmove(scenes, pool[0], C.sizeof(scenes))
+    C.memmove(scenes, packed, C.sizeof(scenes))
     steps = 20
     actions = np.ascontiguousarray(np.random.RandomState(1234).randint(0, 18, size=(steps, n_envs)), np.int32)
     ck = C.c_uint64(0)
     t0 = time.perf_counter()
     lib.orc_bench_rollout(scenes, n_envs, steps, actions.ctypes.data, n_threads, 1, C.byref(ck))
     dt = time.perf_counter() - t0
-    rate = n_envs * steps / dt
     # scale the sample so that the measured run lasts about `seconds_target`
     steps2 = int(max(20, min(6000, steps * seconds_target / max(dt, 1e-3))))
     actions = np.ascontiguousarray(np.random.RandomState(1234).randint(0, 18, size=(steps2, n_envs)), np.int32)
@@ -137,8 +167,9 @@ def cpu_baseline(n_threads, seconds_target=12.0):
     lib.orc_bench_rollout(scenes, n_envs, steps2, actions.ctypes.data, n_threads, 1, C.byref(ck))
     dt = time.perf_counter() - t0
     rate = n_envs * steps2 / dt
+    what = ids[0] if len(ids) == 1 else f'{len(ids)} benchmark ids'
     return {'value': rate, 'unit': UNIT, 'cores': n_threads, 'kind': 'port',
-            'sample': f'{n_envs} envs x {steps2} steps of {ENV_ID} (oracle C port of the pymunk+pygame+cv2 path, '
+            'sample': f'{n_envs} envs x {steps2} steps of {what} (oracle C port of the pymunk+pygame+cv2 path, '
                       f'allo+ego 384^2 render, 3 resizes), {dt:.1f} s'}, n_envs * steps2, dt
 
 
@@ -146,11 +177,12 @@ def run_reference(args, rank, world):
     """--impl reference: the CPU path on all host cores, rank 0 only."""
     if rank != 0:
         return
+    wl = WORKLOADS[args.workload]
     n_threads = host_cores()
     per_step_s = max(2.0, min(20.0, 150.0 / max(args.steps + args.warmup, 1)))
     times, units = [], []
     for i in range(args.warmup + args.steps):
-        cb, n_units, dt = cpu_baseline(n_threads, seconds_target=per_step_s)
+        cb, n_units, dt = cpu_baseline(n_threads, args.workload, seconds_target=per_step_s)
         if i >= args.warmup:
             times.append(dt); units.append(n_units)
     value = sum(units) / sum(times)
@@ -159,13 +191,53 @@ def run_reference(args, rank, world):
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': 1e3 * sum(times) / len(times), 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': f'{ENV_ID} (BASELINE.json configs[1]); each step = a bounded CPU sample: {cb["sample"]}',
+        'config': {'workload': f'{args.workload}: {wl["label"]}; each step = a bounded CPU sample: {cb["sample"]}',
                    'note': 'reference python path (pymunk/pygame/gym) not installable here; oracle C port timed'},
         'cpu_baseline': cb,
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def make_workload_env(m, wl, B, rank, world, local_rank):
+    """The rank's env batch of a workload, reset, phased (pre-roll) and ready to step.  Returns (env, description)."""
+    from magical_b200 import shard
+    ids = workload_ids(m, wl)
+    if len(ids) == 1:
+        env = m.make(ids[0], num_envs=B, device=local_rank, seed=rank * B, obs_keys=('past_obs',))
+        local_ids = None
+    else:
+        # the global batch is the id list repeated round-robin; every rank owns a contiguous block of it, sorted by id
+        # inside the rank so that neighbouring physics lanes see the same task layout (shard.shard_env_ids)
+        global_ids = [ids[i % len(ids)] for i in range(world * B)]
+        gidx, local_ids = shard.shard_env_ids(global_ids, rank, world)
+        env = m.make_mixed([i.replace('-LoRes4E', '') for i in local_ids], device=local_rank, seed=rank * B,
+                           preproc='LoRes4E', obs_keys=('past_obs',))
+    env.placement_retries = 64         # what a reference roll-out loop does after a PlacementError: reset() again
+    force = wl.get('force_blocks')
+    if force is None:
+        env.reset()
+    else:
+        # CountPlus at its maximum: the registered id draws 7..10 blocks; keep the draws with `force` blocks as a pool
+        # (reference RNG and placement sampler) and restart finished envs from it in turn
+        raw = np.frombuffer(env._sample_many(np.arange(B), packed=True), np.uint8).reshape(B, -1)
+        pool = raw[raw.view(np.int32)[:, SCENE_NBLOCKS_WORD] == force].copy()
+        assert len(pool) >= 64, len(pool)
+        cursor = {'k': 0}
+
+        def from_pool(finished):
+            k = cursor['k']
+            cursor['k'] = (k + len(finished)) % len(pool)
+            return pool[(k + np.arange(len(finished))) % len(pool)]
+
+        env.reset_source = from_pool
+        first = np.ascontiguousarray(pool[np.arange(B) % len(pool)])
+        env.set_scenes_packed(np.arange(B), (C.c_uint8 * first.size).from_buffer(first), B)
+        from magical_b200 import _lib as L
+        L.check(env._h, env._lib.mg_reset_obs(env._h, env._obs.data_ptr(), env._stream()))
+        env._needs_reset = False
+    return env, local_ids
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -191,78 +263,66 @@ def run_gpu(args, rank, world, local_rank):
             os.dup2(saved_stdout, 1)
             os.close(saved_stdout)
     m.register_envs()
-    B = args.envs
+    wl = WORKLOADS[args.workload]
+    B = args.envs or wl['envs']
     K, W = args.steps, args.warmup
-    total_steps = 3 * (W + K) + 8
-    horizon = m.spec(ENV_ID)['max_episode_steps']
-    env = m.make(ENV_ID, num_envs=B, device=local_rank, seed=rank * B, obs_keys=('past_obs',))
-    env.auto_reset = False
-    ids = np.arange(B, dtype=np.int32)
+    env, local_ids = make_workload_env(m, wl, B, rank, world, local_rank)
+    horizons = env._horizons
+    Hmax = int(horizons.max())
+    Kk = max(3, min(K, 40))       # per-kernel timing pass
+    Ka = max(3, min(K, 40))       # public-API arm
+    Ke = max(3, min(K, 20))       # end-to-end arm
+    total_steps = Hmax + W + K + Kk + Ka + Ke + 16
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
-    actions = torch.randint(0, 18, (total_steps, B), dtype=torch.int32, device=dev, generator=gen)
-    scores_all = torch.zeros(world * B, dtype=torch.float32, device=dev)
-    state = {'episode': 0, 't': 0}
-    lib, h = env._lib, env._h
-    from magical_b200 import _lib as L
-    obs, rew, done, score = env._obs, env._reward, env._done, env._score
+    # scripted random actions, resident in HBM; re-used cyclically past 512 steps (the pre-roll of long horizons)
+    T_act = min(total_steps, 512)
+    actions = torch.randint(0, 18, (T_act, B), dtype=torch.int32, device=dev, generator=gen)
+    rew = torch.zeros(B, dtype=torch.float32, device=dev)
+    done = torch.zeros(B, dtype=torch.uint8, device=dev)
+    score = [torch.zeros(B, dtype=torch.float32, device=dev) for _ in range(2)]
+    scores_all = [torch.zeros(world * B, dtype=torch.float32, device=dev) for _ in range(2)]
+    works = [None, None]
+    state = {'t': 0}
     stream = torch.cuda.current_stream(dev)
 
-    # initial states of the next episode: the native reset engine (every env on its own RandomState stream)
-    # on host threads, started as soon as the previous reset is installed so that it runs under the episode
-    import threading
-    feeder = {'thread': None, 'scenes': None}
-
-    def feed():
-        feeder['scenes'] = env._sample_many(ids, packed=True)
-
-    def start_feed():
-        feeder['thread'] = threading.Thread(target=feed)
-        feeder['thread'].start()
-
-    def reset_all():
-        feeder['thread'].join()
-        env.set_scenes_packed(ids, feeder['scenes'], B)
-        state['episode'] += 1
-        start_feed()
-
-    start_feed()
-
-    def dev_step():
-        """one pass of the hot path, inputs resident in HBM"""
+    def dev_step(restart=None):
+        """one pass of the hot path, inputs resident in HBM: resets of the finishing envs queued (host), one mg_step,
+        and the ranks' eval scores of this step all-gathered over NCCL while the next step runs"""
         t = state['t']
-        st = stream.cuda_stream
-        if env._episode_steps[0] + 1 < horizon:
-            # no episode ends on this step: the one-call step of the C ABI
-            L.check(h, lib.mg_step(h, actions[t].data_ptr(), obs.data_ptr(), rew.data_ptr(), done.data_ptr(), score.data_ptr(), st))
-            env._episode_steps += 1
-            state['t'] = t + 1
-            return
-        L.check(h, lib.mg_step_physics(h, actions[t].data_ptr(), rew.data_ptr(), done.data_ptr(), score.data_ptr(), st))
-        env._episode_steps += 1
-        if env._episode_steps[0] >= horizon:
-            # episode scores leave the device path here: all-gather over ranks (north_star), then reset
-            if world > 1:
-                dist.all_gather_into_tensor(scores_all, score)
-            reset_all()
-        L.check(h, lib.mg_step_render(h, obs.data_ptr(), st))
+        p = t & 1
+        if works[p] is not None:
+            works[p].wait()                 # stream-level: score[p] / scores_all[p] are free again
+        env.step_into(actions[t % T_act], rew, done, score[p], restart=restart)
+        if world > 1:
+            works[p] = dist.all_gather_into_tensor(scores_all[p], score[p], async_op=True)
         state['t'] = t + 1
 
     def sync_all():
+        for p in range(2):
+            if works[p] is not None:
+                works[p].wait()
+                works[p] = None
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    reset_all()
-    L.check(h, lib.mg_reset_obs(h, obs.data_ptr(), stream.cuda_stream))
+    # pre-roll (untimed): env i restarts i mod horizon steps into its first episode, which spreads the episode phases
+    # evenly; from then on about B / horizon envs finish on every step
+    offs = np.arange(B) % horizons
+    for t in range(1, Hmax):
+        dev_step(restart=np.nonzero(offs == t)[0])
     for _ in range(W):
         dev_step()
     sync_all()
     clocks = ClockSampler(local_rank) if rank == 0 else None
     launches0 = env.launch_count()
+    resets0 = int(env._abs_step)
+    n_fin = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(K):
+        n_fin += int((env._episode_steps + 1 >= horizons).sum())
         dev_step()
     e1.record(stream)
     sync_all()
@@ -271,7 +331,6 @@ def run_gpu(args, rank, world, local_rank):
     # per-kernel durations for the roofline: the same steps again with the library's CUDA-event timers on, which
     # also serialises the step's kernels (in the timed region above mg_step renders finished parts of the batch
     # under the physics tail of the others, so a render launch there has no duration of its own)
-    Kk = max(3, min(K, 40))
     env.set_timing(True)
     env.kernel_ms(0); env.kernel_ms(1)
     for _ in range(Kk):
@@ -287,7 +346,23 @@ def run_gpu(args, rank, world, local_rank):
     ms_max = float(t_ms.item())
     value = world * B * K / (ms_max / 1e3)
 
-    # ---- e2e: the C-ABI call with HOST buffers (pinned): H2D actions, D2H obs/reward/done/score every step
+    # ---- the same loop through the public API: BatchedMagicalEnv.step (auto-reset, tensors cloned per step)
+    sync_all()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(stream)
+    for _ in range(Ka):
+        env.step(actions[state['t'] % T_act])
+        state['t'] += 1
+    a1.record(stream)
+    sync_all()
+    api_ms = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(api_ms, op=dist.ReduceOp.MAX)
+    api_value = world * B * Ka / (float(api_ms.item()) / 1e3)
+
+    # ---- e2e: the C-ABI call with HOST buffers (pinned): H2D actions, D2H obs/reward/done/score every step,
+    # finishing envs restarted inside the call as above
+    obs = env._obs
     a_host = actions.cpu().pin_memory()
     obs_host = torch.empty(obs.shape, dtype=torch.uint8).pin_memory()
     rew_host = torch.empty(B, dtype=torch.float32).pin_memory()
@@ -296,15 +371,12 @@ def run_gpu(args, rank, world, local_rank):
 
     def host_step():
         t = state['t']
-        env.step_host(a_host[t], obs_host, rew_host, done_host, score_host)
-        if env._episode_steps[0] >= horizon:
-            reset_all()
+        env.step_host(a_host[t % T_act], obs_host, rew_host, done_host, score_host)
         state['t'] = t + 1
 
     for _ in range(min(W, 3)):
         host_step()
     sync_all()
-    Ke = max(3, min(K, 20))
     t0 = time.perf_counter()
     for _ in range(Ke):
         host_step()
@@ -313,6 +385,7 @@ def run_gpu(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = world * B * Ke / float(e2e_s.item())
+    status = env.status()
     if rank == 0:
         peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
         if os.path.exists(peaks_path):
@@ -321,27 +394,35 @@ def run_gpu(args, rank, world, local_rank):
             peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
         rend_avg_ms = rend_ms / max(rend_n, 1)
         achieved = B * OBS_BYTES_PER_ENV / (rend_avg_ms * 1e-3) / 1e9
+        step_gbs = value / world * OBS_BYTES_PER_ENV / 1e9
         cb = None
         if world == 1 and not args.no_cpu_baseline:
-            cb, _, _ = cpu_baseline(host_cores())
+            cb, _, _ = cpu_baseline(host_cores(), args.workload)
+        ids = workload_ids(m, wl)
+        what = ids[0] if len(ids) == 1 else f'{len(ids)} benchmark ids (8 tasks x all variants) mixed, sharded by env index'
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W,
             'ms_per_step': ms_max / K, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': f'{ENV_ID} x {B} envs per GPU (BASELINE.json configs[1]), scripted random actions, '
-                                   f'horizon {horizon}, resets inside the timed region (native reset engine on host threads, sampled while the previous episode runs)',
+            'config': {'workload': f'{args.workload}: {what} x {B} envs per GPU ({wl["label"]}), scripted random actions, '
+                                   f'horizons {sorted(set(horizons.tolist()))}, episodes phased so that ~B/horizon envs finish on every step: '
+                                   f'{n_fin} episode ends + restarts inside the {K} timed steps on rank 0 (mg_queue_resets; scenes from the reset feeder thread, reference RNG)'
+                                   + (f'; per-step NCCL all-gather of {world} x {B} eval scores' if world > 1 else ''),
                        'envs_per_gpu': B, 'obs': 'u8[B,96,96,12] past_obs (4 ego frames)',
                        'l2': f'per-step working set (obs {B * OBS_BYTES_PER_ENV / 1e6:.0f} MB + rings + state) exceeds the 126 MB L2',
-                       'parallelism': f'env-sharded x{world}, no data-path collective'},
+                       'parallelism': f'env-sharded x{world}, no data-path collective; score all-gather only',
+                       'episode_ends_in_timed_region': n_fin, 'status_flags_raised': int((status != 0).sum())},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                         'frac_step': step_gbs / peak, 'achieved_step': step_gbs,
                          'traffic': B * NCU_DRAM_BYTES_PER_ENV, 'traffic_source': NCU_TRAFFIC_SOURCE,
                          'kernel': 'mg_render_kernel', 'peak_source': peak_src,
                          'kernel_ms_avg': rend_avg_ms, 'physics_kernel_ms_avg': phys_ms / max(phys_n, 1),
                          'kernel_timing': f'CUDA events around every launch over {Kk} further steps of the same roll-out with the step\'s kernels serialised (mg_set_timing); in the timed region the render launches of finished parts overlap the physics tail',
-                         'note': 'algorithmic bytes = 110592 B x envs per launch; the kernel is issue/latency-bound, not HBM-bound'},
+                         'note': 'frac: algorithmic bytes (110592 B x envs per launch) / render-kernel time; frac_step: SURVEY 8(d) / BASELINE.md 4 definition, env-steps/s per GPU x 110592 B / peak (whole step). The kernels are issue/latency-bound, not HBM-bound'},
             'cpu_baseline': cb,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * B * 4,
                     'd2h_bytes_per_step': world * (obs.numel() + B * 9), 'steps': Ke},
+            'api': {'value': api_value, 'unit': UNIT, 'steps': Ka, 'call': 'BatchedMagicalEnv.step (auto_reset=True, device tensors)'},
             'gpu_launches': launches,
             'clocks': clock_info,
         }
@@ -357,7 +438,8 @@ def main():
     ap.add_argument('--steps', type=int, default=160)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--envs', type=int, default=ENVS_PER_GPU)
+    ap.add_argument('--workload', default='cfg1', choices=sorted(WORKLOADS))
+    ap.add_argument('--envs', type=int, default=0, help='envs per GPU (default: the workload\'s)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))

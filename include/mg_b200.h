@@ -10,6 +10,9 @@
  *                             + lores_*_entry_point wrapper stack    magical/benchmarks/__init__.py:232-266
  *   mg_set_scenes             BaseEnv.reset (space + entities built  magical/base_env.py:190-246
  *                             from host-sampled on_reset() results)  magical/benchmarks/<task>.py on_reset
+ *   mg_queue_resets           the roll-out loop `while not done: env.step(a)` ... `env.reset()` of
+ *                             magical/misc/benchmark_env_perf.py:12-18 and evaluation.py, batched: envs that finish on
+ *                             the next step start their next episode inside that step (BaseEnv.reset, base_env.py:190-246)
  *   mg_step / mg_step_host    BaseEnv.step                           magical/base_env.py:267-307
  *                               Robot.set_action / Robot.update      magical/entities.py:435-476
  *                               pm.Space.step x10                    magical/base_env.py:248-255
@@ -89,6 +92,15 @@ const char *mg_last_error(const mg_handle *h); /* h may be NULL: error of the la
  * The host arrays are copied before the call returns (they may be pageable and reused at once); the upload and the
  * initialisation kernel run on `stream` without draining it. */
 int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream);
+
+/* Queue resets for the NEXT step (auto-reset): the `n` envs are re-initialised to `scenes_host` after the physics of
+ * the next mg_step / mg_step_host / mg_step_physics + mg_step_render and before its render, so that the step returns
+ * reward / done / eval_score of the finished episode and the first observation of the new one (what a roll-out loop
+ * that calls env.reset() on done sees).  Unlike mg_step_physics + mg_set_scenes + mg_step_render this keeps the one-call
+ * step, whose parts render under the physics tail of the others.  The host arrays are copied before the call returns.
+ * One call per step: a second call before a step has consumed the first, and mg_set_scenes in between, are
+ * rejected with MG_ERR_ARG. */
+int mg_queue_resets(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream);
 
 /* Render the current state of every env into the frame stacks and write the stacked
  * observation (what reset() returns).  obs_dev: u8 [B,96,96,3*n_groups] (or CHW). */

@@ -74,6 +74,7 @@ SYMBOLS = {
     'mg_destroy': (C.c_int, [_VP]),
     'mg_last_error': (C.c_char_p, [_VP]),
     'mg_set_scenes': (C.c_int, [_VP, _VP, C.c_int, _VP, _VP]),
+    'mg_queue_resets': (C.c_int, [_VP, _VP, C.c_int, _VP, _VP]),
     'mg_reset_obs': (C.c_int, [_VP, _VP, _VP]),
     'mg_step': (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'mg_step_physics': (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),

@@ -50,6 +50,7 @@ struct mg_handle {
      * runs on own_stream and must not start before it (the caller need not synchronise between the two) */
     cudaEvent_t caller_ev;
     int caller_ev_used;
+    int pending_queued;                      /* mg_queue_resets ran and no step has applied its resets yet */
     /* accounting */
     int64_t launches;
     int timing;
@@ -118,6 +119,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaMalloc(&h->S.prims, (size_t)B * MG_MAX_PRIMS * sizeof(MgPrim)));
     CK(h, cudaMalloc(&h->S.n_prims, (size_t)B * sizeof(int)));
     CK(h, cudaMemset(h->S.n_prims, 0, (size_t)B * sizeof(int)));
+    CK(h, cudaMalloc(&h->S.pending, (size_t)B * sizeof(int)));
+    CK(h, cudaMemset(h->S.pending, 0xff, (size_t)B * sizeof(int)));       /* -1: no reset queued */
     CK(h, cudaMalloc(&h->S.status, (size_t)B * sizeof(int)));
     CK(h, cudaMemset(h->S.status, 0, (size_t)B * sizeof(int)));
     CK(h, cudaMalloc(&h->S.poses, (size_t)B * MG_POSE_STRIDE * sizeof(double)));
@@ -135,6 +138,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     h->S.num_envs = B;
     CK(h, cudaMalloc(&h->scene_stage_dev, (size_t)B * sizeof(mg_scene)));
     CK(h, cudaMalloc(&h->ids_stage_dev, (size_t)B * sizeof(int32_t)));
+    h->S.pending_scenes = h->scene_stage_dev;
+    h->pending_queued = 0;
     for (int k = 0; k < 2; k++) {
         CK(h, cudaMallocHost(&h->scene_stage_host[k], (size_t)B * sizeof(mg_scene)));
         CK(h, cudaMallocHost(&h->ids_stage_host[k], (size_t)B * sizeof(int32_t)));
@@ -178,7 +183,7 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     cudaFree(h->S.dstate); cudaFree(h->S.istate); cudaFree(h->S.scenes); cudaFree(h->S.prims);
-    cudaFree(h->S.n_prims); cudaFree(h->S.status); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
+    cudaFree(h->S.n_prims); cudaFree(h->S.status); cudaFree(h->S.pending); cudaFree(h->S.poses); cudaFree(h->S.ring[0]); cudaFree(h->S.ring[1]);
     for (int v = 0; v < 2; v++) { cudaFree(h->S.sprims[v]); cudaFree(h->S.sverts[v]); cudaFree(h->S.dashv[v]); }
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
@@ -203,8 +208,37 @@ static void mark_caller(mg_handle *h, cudaStream_t st)
 
 static int check_launch(mg_handle *h, const char *what)
 {
-    cudaError_t e = cudaGetLastError();
+    /* MG_DEBUG_SYNC=1: drain the device after every group of launches so that an asynchronous fault is reported by
+     * the call that caused it (debugging only: it serialises everything) */
+    static const bool debug_sync = getenv("MG_DEBUG_SYNC") && atoi(getenv("MG_DEBUG_SYNC")) != 0;
+    cudaError_t e = debug_sync ? cudaDeviceSynchronize() : cudaSuccess;
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, MG_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return MG_OK;
+}
+
+/* validate and copy `n` scenes (+ ids) into the pinned staging slot and start their upload on `st`; the caller
+ * launches the kernel that consumes the device staging and then calls stage_done */
+static int stage_upload(mg_handle *h, const char *who, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, cudaStream_t st, int *slot_out)
+{
+    for (int i = 0; i < n; i++) {
+        if (env_ids_host && (env_ids_host[i] < 0 || env_ids_host[i] >= h->cfg.num_envs))
+            return fail(h, MG_ERR_ARG, std::string(who) + ": env id out of range");
+        const mg_scene &s = scenes_host[i];
+        if (s.n_blocks < 0 || s.n_blocks > MG_MAX_BLOCKS || s.n_goals < 0 || s.n_goals > MG_MAX_GOALS ||
+            s.task < 0 || s.task >= MG_NUM_TASKS)
+            return fail(h, MG_ERR_ARG, std::string(who) + ": scene out of range");
+    }
+    for (int i = 0; i < n; i++) h->max_blocks = scenes_host[i].n_blocks > h->max_blocks ? scenes_host[i].n_blocks : h->max_blocks;
+    const int slot = h->stage_slot ^= 1;
+    if (h->stage_used[slot]) CK(h, cudaEventSynchronize(h->stage_ev[slot]));          /* long done: two calls ago */
+    memcpy(h->scene_stage_host[slot], scenes_host, (size_t)n * sizeof(mg_scene));
+    if (env_ids_host) memcpy(h->ids_stage_host[slot], env_ids_host, (size_t)n * sizeof(int32_t));
+    /* the device side of the staging is one buffer: order this call behind the kernel that read the previous upload */
+    if (h->stage_used[slot ^ 1]) CK(h, cudaStreamWaitEvent(st, h->stage_ev[slot ^ 1], 0));
+    CK(h, cudaMemcpyAsync(h->scene_stage_dev, h->scene_stage_host[slot], (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
+    if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, h->ids_stage_host[slot], (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    *slot_out = slot;
     return MG_OK;
 }
 
@@ -212,31 +246,49 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
 {
     if (!h || !scenes_host || n < 0 || n > h->cfg.num_envs) return fail(h, MG_ERR_ARG, "mg_set_scenes: bad argument");
     if (n == 0) return MG_OK;
+    if (h->pending_queued) return fail(h, MG_ERR_ARG, "mg_set_scenes: resets queued with mg_queue_resets are still waiting for a step");
     cudaStream_t st = (cudaStream_t)stream;
     CK(h, cudaSetDevice(h->cfg.device));
-    for (int i = 0; i < n; i++) {
-        if (env_ids_host && (env_ids_host[i] < 0 || env_ids_host[i] >= h->cfg.num_envs))
-            return fail(h, MG_ERR_ARG, "mg_set_scenes: env id out of range");
-        const mg_scene &s = scenes_host[i];
-        if (s.n_blocks < 0 || s.n_blocks > MG_MAX_BLOCKS || s.n_goals < 0 || s.n_goals > MG_MAX_GOALS ||
-            s.task < 0 || s.task >= MG_NUM_TASKS)
-            return fail(h, MG_ERR_ARG, "mg_set_scenes: scene out of range");
-    }
-    for (int i = 0; i < n; i++) h->max_blocks = scenes_host[i].n_blocks > h->max_blocks ? scenes_host[i].n_blocks : h->max_blocks;
-    const int slot = h->stage_slot ^= 1;
-    if (h->stage_used[slot]) CK(h, cudaEventSynchronize(h->stage_ev[slot]));          /* long done: two calls ago */
-    memcpy(h->scene_stage_host[slot], scenes_host, (size_t)n * sizeof(mg_scene));
-    if (env_ids_host) memcpy(h->ids_stage_host[slot], env_ids_host, (size_t)n * sizeof(int32_t));
-    /* the device side of the staging is one buffer: order this call behind the init kernel of the previous one */
-    if (h->stage_used[slot ^ 1]) CK(h, cudaStreamWaitEvent(st, h->stage_ev[slot ^ 1], 0));
-    CK(h, cudaMemcpyAsync(h->scene_stage_dev, h->scene_stage_host[slot], (size_t)n * sizeof(mg_scene), cudaMemcpyHostToDevice, st));
-    if (env_ids_host) CK(h, cudaMemcpyAsync(h->ids_stage_dev, h->ids_stage_host[slot], (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    int slot = 0;
+    int rc = stage_upload(h, "mg_set_scenes", env_ids_host, n, scenes_host, st, &slot);
+    if (rc != MG_OK) return rc;
     mg_launch_init(h->S, h->scene_stage_dev, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
     h->launches++;
     CK(h, cudaEventRecord(h->stage_ev[slot], st));
     h->stage_used[slot] = 1;
     mark_caller(h, st);
     return check_launch(h, "mg_init_kernel");
+}
+
+/* resets for the NEXT step: uploaded and marked now, applied by that step's geometry pre-pass after its physics
+ * (the staged scenes stay in place until then: one queue per step) */
+extern "C" int mg_queue_resets(mg_handle *h, const int32_t *env_ids_host, int n, const mg_scene *scenes_host, void *stream)
+{
+    if (!h || n < 0 || n > h->cfg.num_envs || (n > 0 && !scenes_host)) return fail(h, MG_ERR_ARG, "mg_queue_resets: bad argument");
+    if (n == 0) return MG_OK;
+    if (h->pending_queued) return fail(h, MG_ERR_ARG, "mg_queue_resets: resets are already queued for the next step (one call per step)");
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(h, cudaSetDevice(h->cfg.device));
+    int slot = 0;
+    int rc = stage_upload(h, "mg_queue_resets", env_ids_host, n, scenes_host, st, &slot);
+    if (rc != MG_OK) return rc;
+    mg_launch_mark_pending(h->S, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
+    h->launches++;
+    /* the device staging is read by the step that applies the resets: its end is recorded by that step (pending_done) */
+    h->pending_queued = 1 + slot;
+    mark_caller(h, st);
+    return check_launch(h, "mg_mark_pending_kernel");
+}
+
+/* a step has launched the render work that applies the queued resets: the staging may be reused after it */
+static int pending_done(mg_handle *h, cudaStream_t st)
+{
+    if (!h->pending_queued) return MG_OK;
+    const int slot = h->pending_queued - 1;
+    CK(h, cudaEventRecord(h->stage_ev[slot], st));
+    h->stage_used[slot] = 1;
+    h->pending_queued = 0;
+    return MG_OK;
 }
 
 /* per-kernel timing: event pairs are recorded on the launching stream without synchronising and
@@ -288,7 +340,7 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
     for (int v = 0; v < 2; v++) {
         if (!h->spec.render_view[v]) continue;
         bool fuse = h->fused && v == last_view && obs_dev;
-        mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, 0, h->cfg.num_envs, st);
+        mg_launch_render_push(h->S, v, h->slots[v], fuse ? &h->spec : nullptr, h->slots, obs_dev, 0, h->cfg.num_envs, st, h->pending_queued != 0);
         nl++;
     }
     time_end(h, 1, nl, st);      /* one timed unit = geometry + raster launch of one view */
@@ -296,6 +348,7 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
     if (!h->fused && obs_dev && h->spec.n_groups > 0) { mg_launch_compose(h->S, h->spec, h->slots, obs_dev, st); nl++; }
     mg_launch_clear_fresh(h->S, st); nl++;
     h->launches += nl;
+    { int rc = pending_done(h, st); if (rc != MG_OK) return rc; }
     mark_caller(h, st);
     return check_launch(h, "mg_render_kernel");
 }
@@ -338,12 +391,13 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
         cudaStream_t sk = h->part_stream[k];
         MgDeviceState Sr = h->S;
         if (ordered) Sr.perm = h->perm_dev;
-        mg_launch_render_push(Sr, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk);
+        mg_launch_render_push(Sr, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk, h->pending_queued != 0);
         CK(h, cudaEventRecord(h->part_done[k], sk));
         CK(h, cudaStreamWaitEvent(st, h->part_done[k], 0));
     }
     mg_launch_clear_fresh(h->S, st);
     h->launches += 3 * P + 1 + (ordered ? 1 : 0);
+    { int rc = pending_done(h, st); if (rc != MG_OK) return rc; }
     mark_caller(h, st);
     return check_launch(h, "mg_step (parts)");
 }
@@ -381,7 +435,7 @@ extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *
         const size_t env_bytes = h->obs_bytes / (size_t)B;
         for (int c = 0; c < MG_HOST_CHUNKS; c++) {
             const int e0 = (int)((long long)B * c / MG_HOST_CHUNKS), e1 = (int)((long long)B * (c + 1) / MG_HOST_CHUNKS);
-            mg_launch_render_push(h->S, view, h->slots[view], &h->spec, h->slots, h->obs_dev, e0, e1, st);
+            mg_launch_render_push(h->S, view, h->slots[view], &h->spec, h->slots, h->obs_dev, e0, e1, st, h->pending_queued != 0);
             CK(h, cudaEventRecord(h->chunk_done[c], st));
             CK(h, cudaStreamWaitEvent(h->copy_stream, h->chunk_done[c], 0));
             CK(h, cudaMemcpyAsync(obs_host + (size_t)e0 * env_bytes, h->obs_dev + (size_t)e0 * env_bytes,
@@ -389,6 +443,8 @@ extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *
         }
         mg_launch_clear_fresh(h->S, st);
         h->launches += 2 * MG_HOST_CHUNKS + 1;
+        rc = pending_done(h, st);
+        if (rc != MG_OK) return rc;
         rc = check_launch(h, "mg_render_kernel");
         if (rc != MG_OK) return rc;
     } else {

@@ -30,6 +30,10 @@ struct MgDeviceState {
      * their k-th work slot, so that a part of the batch can be any set of envs (mg_step groups envs by contact load) */
     const int *perm;
     int *status;             /* [B] sticky MG_STATUS_* bits (NULL: not collected) */
+    /* resets queued with mg_queue_resets: pending[env] = index into pending_scenes, or -1.  The geometry pre-pass of
+     * the step path applies them (init_env) after the step's physics and before the env is rendered. */
+    int *pending;
+    const mg_scene *pending_scenes;
 };
 #define MG_MAX_DEVICES 64    /* CUDA ordinals the per-device launch attributes are tracked for */
 
@@ -42,6 +46,7 @@ struct MgObsSpec {
 };
 
 void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st);
+void mg_launch_mark_pending(const MgDeviceState &S, const int32_t *env_ids_dev, int n, cudaStream_t st);
 /* max_blocks: largest block count of any env in the batch (sizes the per-env shared-memory copy) */
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st);
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);
@@ -49,10 +54,10 @@ void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaS
  * same kernel also writes the stacked HWC observation (slots[v] = newest slot of view v); envs
  * [env_begin, env_end) only, so that a host copy of one part can overlap the rendering of the next */
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
-                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st);
+                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st, int apply_pending = 0);
 /* transform every primitive of every env into the screen space of `view` (must precede the render launches
  * of that view whenever poses or scenes changed) */
-void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st);
+void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st, int apply_pending = 0);
 /* compose the stacked observation from the rings (any view mix, HWC or CHW) */
 void mg_launch_compose(const MgDeviceState &S, const MgObsSpec &spec, const int *slots, uint8_t *obs, cudaStream_t st);
 /* clear the per-env "fresh" flag after all views were pushed */

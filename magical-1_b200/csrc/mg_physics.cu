@@ -27,212 +27,22 @@
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
 
-/* d / i: the env's double and int fields up to (not including) the arbiter cache -- HBM, or the step
- * kernel's shared-memory copy (bodies at d, constraints at dc); da / ia: the env's full field arrays in HBM (arbiters, goals, target) */
-struct EnvRef { double *d; double *dc; int *i; double *da; int *ia; };
-#define DF(e, f) ((e).d[(size_t)(f) * MG_GROUP])
-#define IF(e, f) ((e).i[(size_t)(f) * MG_GROUP])
-#define DGF(e, f) ((e).da[(size_t)(f) * MG_GROUP])
-#define BF(e, b, f) DF(e, D_BODY0 + (b) * B_NF + (f))
-#define CF(e, c, f) ((e).dc[(size_t)((c) * C_NF + (f)) * MG_GROUP])
-#define AF(e, a, f) DGF(e, D_ARB0 + (a) * A_NF + (f))
-#define ACF(e, a, k, f) DGF(e, D_ARB0 + (a) * A_NF + A_CON0 + (k) * AC_NF + (f))
-#define AIF(e, a, f) ((e).ia[(size_t)(I_ARB0 + (a) * 4 + (f)) * MG_GROUP])
+#include "mg_envref.cuh"
 
-__device__ __forceinline__ EnvRef env_ref(double *dstate, int *istate, int env)
-{
-    EnvRef e;
-    e.d = e.da = dstate + mg_field_index(env, D_NF, 0);
-    e.dc = e.d + (size_t)D_CON0 * MG_GROUP;
-    e.i = e.ia = istate + mg_field_index(env, I_NF, 0);
-    return e;
-}
-
-#define MG_DT ((1.0 / 8) / 10)   /* fps = 8 (benchmarks/__init__.py:435), phys_steps = 10 (base_env.py:249) */
-
-/* ------------------------------------------------------------------ reset expansion */
-
-__device__ void init_body(EnvRef e, int b, int dynamic, double m, double i, double x, double y, double a)
-{
-    for (int f = 0; f < B_NF; f++) BF(e, b, f) = 0.0;
-    BF(e, b, B_PX) = x; BF(e, b, B_PY) = y; BF(e, b, B_A) = a;
-    double s, c;
-    mg_sincos(a, &s, &c);
-    BF(e, b, B_RX) = c; BF(e, b, B_RY) = s;
-    BF(e, b, B_MINV) = dynamic ? 1.0 / m : 0.0;
-    BF(e, b, B_IINV) = dynamic ? 1.0 / i : 0.0;
-}
-
-__device__ int add_con(EnvRef e, int kind, int a, int b, double max_force, double max_bias, double bc)
-{
-    int c = IF(e, I_NCON);
-    IF(e, I_NCON) = c + 1;
-    IF(e, I_CON0 + c) = kind | (a << 8) | (b << 16);
-    for (int f = 0; f < C_NF; f++) CF(e, c, f) = 0.0;
-    CF(e, c, C_JMAX) = max_force * MG_DT;
-    CF(e, c, C_MAXBIAS) = max_bias;
-    CF(e, c, C_BC) = bc;
-    return c;
-}
-
-__device__ void add_shape(EnvRef e, int tpl, int body, int ent)
-{
-    int s = IF(e, I_NSHAPES);
-    IF(e, I_NSHAPES) = s + 1;
-    IF(e, I_SHAPE0 + s) = tpl | (body << 8) | (ent << 16);
-}
-
-__device__ void add_prim(MgPrim *prims, int *n, int dl, int chain, int body, int fill, int outline, int mode, int aux)
-{
-    MgPrim p;
-    p.dl = (uint8_t)dl; p.chain = (uint8_t)chain; p.body = (uint8_t)body; p.fill = (uint8_t)fill;
-    p.outline = (uint8_t)outline; p.mode = (uint8_t)mode; p.aux = (uint8_t)aux; p.pad = 0;
-    prims[(*n)++] = p;
-}
-
-/* Robot.setup (entities.py:238-433) */
-__device__ void setup_robot(EnvRef e, const MgTables *T, const mg_scene *sc, MgPrim *prims, int *np)
-{
-    const double radius = 0.2, mass = 1.0, inf = INFINITY;
-    const int rb = MG_BODY_ROBOT;
-    double inertia = mass * (0.5 * (0.0 * 0.0 + radius * radius) + 0.0);
-    init_body(e, rb + MG_RB_ROBOT, 1, mass, inertia, sc->robot[MG_RB_ROBOT][0], sc->robot[MG_RB_ROBOT][1], sc->robot[MG_RB_ROBOT][2]);
-    init_body(e, rb + MG_RB_CONTROL, 0, 0, 0, sc->robot[MG_RB_CONTROL][0], sc->robot[MG_RB_CONTROL][1], sc->robot[MG_RB_CONTROL][2]);
-    add_con(e, CON_PIVOT, rb + MG_RB_CONTROL, rb + MG_RB_ROBOT, sc->phys[0], 0.0, T->bias_coef_default);
-    int c = add_con(e, CON_GEAR, rb + MG_RB_CONTROL, rb + MG_RB_ROBOT, sc->phys[1], 2.5, 1.0);
-    CF(e, c, C_P0) = 0.0; CF(e, c, C_P1) = 1.0;
-    for (int k = 0; k < 2; k++) {
-        double eye_mass = mass / 10;
-        double eye_inertia = eye_mass * (0.5 * (radius * radius));
-        int pb = rb + MG_RB_PUPIL_L + k;
-        init_body(e, pb, 1, eye_mass, eye_inertia, sc->robot[MG_RB_PUPIL_L + k][0], sc->robot[MG_RB_PUPIL_L + k][1], sc->robot[MG_RB_PUPIL_L + k][2]);
-        c = add_con(e, CON_SPRING, rb + MG_RB_ROBOT, pb, 0.001, 3.0, T->bias_coef_default);
-        CF(e, c, C_P0) = T->spring_w_coef;
-    }
-    for (int k = 0; k < 2; k++) {
-        double side = k == 0 ? -1.0 : 1.0;
-        double lower = k == 0 ? -0.0 : -(M_PI / 8);
-        double upper = k == 0 ? (M_PI / 8) : 0.0;
-        int fb = rb + MG_RB_FINGER_L + k;
-        init_body(e, fb, 1, mass / 8, T->finger_moment[k], sc->robot[MG_RB_FINGER_L + k][0], sc->robot[MG_RB_FINGER_L + k][1], sc->robot[MG_RB_FINGER_L + k][2]);
-        c = add_con(e, CON_PIVOT, rb + MG_RB_ROBOT, fb, inf, inf, 1.0);
-        CF(e, c, C_P0) = side * radius * 0.45; CF(e, c, C_P1) = radius * 0.1;
-        c = add_con(e, CON_LIMIT, rb + MG_RB_ROBOT, fb, inf, inf, 1.0);
-        CF(e, c, C_P0) = lower; CF(e, c, C_P1) = upper;
-        c = add_con(e, CON_MOTOR, rb + MG_RB_ROBOT, fb, sc->phys[2], 0.0, T->bias_coef_default);
-        CF(e, c, C_P0) = 0.0;
-    }
-    add_shape(e, MG_TPL_CIRCLE_ROBOT, rb + MG_RB_ROBOT, MG_ENTID_ROBOT);
-    for (int k = 0; k < 2; k++)
-        for (int part = 0; part < 2; part++)
-            add_shape(e, MG_TPL_FINGER0 + k * 2 + part, rb + MG_RB_FINGER_L + k, MG_ENTID_ROBOT);
-    /* graphics, entities.py:374-433 */
-    for (int k = 0; k < 2; k++)
-        for (int part = 0; part < 2; part++)
-            add_prim(prims, np, MG_DL_FINGER_OUT0 + k * 2 + part, MG_CHAIN_BODY, rb + MG_RB_FINGER_L + k, MG_PAL_GREY, 0, 0, 0);
-    for (int k = 0; k < 2; k++)
-        for (int part = 0; part < 2; part++)
-            add_prim(prims, np, MG_DL_FINGER_IN0 + k * 2 + part, MG_CHAIN_BODY, rb + MG_RB_FINGER_L + k, MG_PAL_GREY_LIGHT, 0, 0, 0);
-    add_prim(prims, np, MG_DL_ROBOT, MG_CHAIN_BODY, rb + MG_RB_ROBOT, MG_PAL_GREY, MG_PAL_GREY_DARK, 1, 0);
-    for (int k = 0; k < 2; k++) {
-        add_prim(prims, np, MG_DL_EYE, MG_CHAIN_EYE, rb + MG_RB_ROBOT, MG_PAL_WHITE, 0, 0, k);
-        add_prim(prims, np, MG_DL_PUPIL, MG_CHAIN_PUPIL, rb + MG_RB_PUPIL_L + k, MG_PAL_PUPIL, 0, 0, k);
-    }
-}
-
-/* Shape.setup (entities.py:610-749) */
-__device__ void setup_block(EnvRef e, const MgTables *T, const mg_scene *sc, int bi, MgPrim *prims, int *np)
-{
-    const mg_block *bl = &sc->blocks[bi];
-    const double mass = 0.5, shape_size = 0.2 * 0.6;
-    int body = MG_BODY_BLOCK0 + bi, ent = MG_ENTID_BLOCK0 + bi;
-    int col = MG_PAL_COLOUR0 + bl->colour, dark = MG_PAL_DARK0 + bl->colour;
-    switch (bl->type) {
-    case MG_SQUARE:
-        init_body(e, body, 1, mass, T->square_moment, bl->x, bl->y, bl->angle);
-        add_shape(e, MG_TPL_SQUARE, body, ent);
-        break;
-    case MG_CIRCLE:
-        init_body(e, body, 1, mass, mass * (0.5 * (shape_size * shape_size)), bl->x, bl->y, bl->angle);
-        add_shape(e, MG_TPL_CIRCLE_BLOCK, body, ent);
-        break;
-    case MG_STAR:
-        init_body(e, body, 1, mass, T->star_moment, bl->x, bl->y, bl->angle);
-        for (int k = 0; k < MG_STAR_PIECES; k++) add_shape(e, MG_TPL_STAR0 + k, body, ent);
-        break;
-    default:
-        init_body(e, body, 1, mass, T->pent_moment, bl->x, bl->y, bl->angle);
-        add_shape(e, MG_TPL_PENT, body, ent);
-        break;
-    }
-    /* floor friction: entities.py:700-708 */
-    add_con(e, CON_PIVOT, 0, body, sc->phys[3], 0.0, T->bias_coef_default);
-    int c = add_con(e, CON_GEAR, 0, body, sc->phys[4], 0.0, T->bias_coef_default);
-    CF(e, c, C_P0) = 0.0; CF(e, c, C_P1) = 1.0;
-    switch (bl->type) {
-    case MG_SQUARE: add_prim(prims, np, MG_DL_SQUARE, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
-    case MG_CIRCLE: add_prim(prims, np, MG_DL_CIRCLE, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
-    case MG_STAR:
-        for (int k = 0; k < MG_STAR_PIECES; k++) add_prim(prims, np, MG_DL_STAR_OUT0 + k, MG_CHAIN_BODY, body, dark, 0, 0, 0);
-        for (int k = 0; k < MG_STAR_PIECES; k++) add_prim(prims, np, MG_DL_STAR_IN0 + k, MG_CHAIN_BODY, body, col, 0, 0, 0);
-        break;
-    default: add_prim(prims, np, MG_DL_PENT, MG_CHAIN_BODY, body, col, dark, 1, 0); break;
-    }
-}
-
-__device__ void export_poses(EnvRef e, double *pose)
-{
-    int nb = IF(e, I_NBODIES);
-    for (int b = 0; b < MG_NB; b++) {
-        double *o = pose + b * MG_POSE_NF;
-        if (b < nb) {
-            o[0] = BF(e, b, B_PX); o[1] = BF(e, b, B_PY); o[2] = BF(e, b, B_A);
-            o[3] = BF(e, b, B_VX); o[4] = BF(e, b, B_VY); o[5] = BF(e, b, B_W);
-            o[6] = BF(e, b, B_RX); o[7] = BF(e, b, B_RY);
-        } else {
-            for (int k = 0; k < MG_POSE_NF; k++) o[k] = 0.0;
-        }
-    }
-}
-
-/* BaseEnv.reset after on_reset(): expand host-sampled scenes into simulation state
- * (magical/base_env.py:190-246; add order arena, goals, [robot], blocks, [robot]). */
+/* BaseEnv.reset after on_reset(): expand host-sampled scenes into simulation state (init_env, mg_envref.cuh) */
 __global__ void mg_init_kernel(MgDeviceState S, const mg_scene *scenes, const int32_t *env_ids, int n)
 {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
-    int env = env_ids ? env_ids[k] : k;
-    const mg_scene *sc = &scenes[k];
-    const MgTables *T = S.tables;
-    EnvRef e = env_ref(S.dstate, S.istate, env);
-    S.scenes[env] = *sc;
-    for (int f = 0; f < I_ARB0; f++) IF(e, f) = 0;
-    IF(e, I_TASK) = sc->task; IF(e, I_HORIZON) = sc->horizon;
-    IF(e, I_NBLOCKS) = sc->n_blocks; IF(e, I_NGOALS) = sc->n_goals;
-    IF(e, I_ROBOT_FIRST) = sc->robot_first; IF(e, I_DEBUG_REWARD) = sc->debug_reward;
-    IF(e, I_TARGET_BLOCK) = sc->target_block; IF(e, I_NVALID) = sc->n_valid_targets;
-    IF(e, I_NBODIES) = 1 + MG_RB_COUNT + sc->n_blocks;
-    IF(e, I_FRESH) = 1;
-    DGF(e, D_TARGET) = sc->target_pos[0]; DGF(e, D_TARGET + 1) = sc->target_pos[1];
-    init_body(e, 0, 0, 0, 0, 0.0, 0.0, 0.0);
-    MgPrim *prims = S.prims + (size_t)env * MG_MAX_PRIMS;
-    int np = 0;
-    for (int w = 0; w < 4; w++) add_shape(e, MG_TPL_WALL0 + w, 0, MG_ENTID_ARENA);
-    add_prim(prims, &np, MG_DL_ARENA, MG_CHAIN_CAM, 0, MG_PAL_WHITE, MG_PAL_GREY, 1, 0);
-    for (int g = 0; g < sc->n_goals; g++) {
-        const mg_goal *go = &sc->goals[g];
-        DGF(e, D_GOAL0 + g * 4 + 0) = go->cx; DGF(e, D_GOAL0 + g * 4 + 1) = go->cy;
-        DGF(e, D_GOAL0 + g * 4 + 2) = go->h;  DGF(e, D_GOAL0 + g * 4 + 3) = go->w;
-        IF(e, I_GOAL0 + g) = go->colour | ((go->want_block + 1) << 8);
-        add_prim(prims, &np, MG_DL_GOAL, MG_CHAIN_GOAL, 0, MG_PAL_LIGHT0 + go->colour, MG_PAL_COLOUR0 + go->colour, 2, g);
-    }
-    for (int b = 0; b < sc->n_blocks; b++)
-        IF(e, I_BLOCK0 + b) = sc->blocks[b].type | (sc->blocks[b].colour << 8) | (sc->blocks[b].role << 16);
-    if (sc->robot_first) setup_robot(e, T, sc, prims, &np);
-    for (int b = 0; b < sc->n_blocks; b++) setup_block(e, T, sc, b, prims, &np);
-    if (!sc->robot_first) setup_robot(e, T, sc, prims, &np);
-    S.n_prims[env] = np;
-    export_poses(e, S.poses + (size_t)env * MG_POSE_STRIDE);
+    init_env(S, &scenes[k], env_ids ? env_ids[k] : k);
+}
+
+/* mg_queue_resets: pending[env] <- index of the env's new scene in the staging array; the geometry pre-pass of the
+ * next step applies it after that step's physics */
+__global__ void mg_mark_pending_kernel(MgDeviceState S, const int32_t *env_ids, int n)
+{
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) S.pending[env_ids ? env_ids[k] : k] = k;
 }
 
 /* ------------------------------------------------------------------ body helpers (chipmunk_private.h) */
@@ -488,16 +298,49 @@ __device__ __noinline__ void tpl_world_bb(const MgTables *T, int tpl, vec2 p, ve
     }
 }
 
+/* ---- live arbiters of the current sub-step.
+ * The arbiter cache (MG_NARB slots per env) lives in HBM: it is large, and only envs in contact touch it.  But the
+ * sequential-impulse iterations read and write every live contact ten times per sub-step, and a global store drops the
+ * line from L1, so with the cache slot as working storage every iteration paid L2 latency on jn / jt / jBias.  The first
+ * MG_ARB_POOL live arbiters of a sub-step therefore work in a shared-memory pool (same A_NF-double layout as a slot):
+ * cpArbiterUpdate writes r1 / r2 / warm-started jn, jt / n / u there, the pre-step and the iterations use it, and after
+ * the last iteration jn / jt -- the only per-contact fields a later step reads back (warm start by contact hash) -- are
+ * copied to the slot.  Live arbiters beyond the pool work in their slot as before.  Same arithmetic either way. */
+#ifndef MG_ARB_POOL
+#define MG_ARB_POOL 8
+#endif
+static_assert(MG_GROUP == 1, "arbiter working storage is addressed as a contiguous A_NF-double block");
+struct ArbRef { double *p; int a, b, count, state; };
+
+__device__ __forceinline__ ArbRef arb_ref(EnvRef e, const unsigned char *order, int q)
+{
+    ArbRef r;
+    if (q < e.apn) {
+        const int w = e.ainfo[q];
+        r.p = e.ap + (size_t)q * A_NF;
+        r.a = w & 255; r.b = (w >> 8) & 255; r.count = (w >> 16) & 255; r.state = (w >> 24) & 255;
+    } else {
+        const int s = order[q];
+        const int key = AIF(e, s, AI_KEY), fl = AIF(e, s, AI_FLAGS);
+        r.p = &AF(e, s, 0);
+        r.a = (key >> 16) & 255; r.b = (key >> 24) & 255; r.count = (fl >> 8) & 255; r.state = fl & 255;
+    }
+    return r;
+}
+#define APF(r, f) ((r).p[(f)])
+#define APC(r, k, f) ((r).p[A_CON0 + (k) * AC_NF + (f)])
+
 /* cpArbiterUpdate for the colliding shapes sa, sb (already in cpShapeType order, infos ia, ib) with
- * manifold m; returns the arbiter slot or -1.  Serial per env: slots are handed out in discovery order. */
-__device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Manifold &m, int stamp)
+ * manifold m; returns the arbiter slot or -1.  Serial per env: slots are handed out in discovery order.
+ * q: index of this arbiter among the live ones of the sub-step (selects the working storage). */
+__device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Manifold &m, int stamp, int q)
 {
     int ba = (ia >> 8) & 255, bb = (ib >> 8) & 255;
     int key = sa | (sb << 8);
     int n_arbs = IF(e, I_NARBS), slot = -1;
     MG_NOUNROLL
-    for (int q = 0; q < n_arbs; q++)
-        if ((AIF(e, q, AI_KEY) & 0xffff) == key) { slot = q; break; }
+    for (int k = 0; k < n_arbs; k++)
+        if ((AIF(e, k, AI_KEY) & 0xffff) == key) { slot = k; break; }
     int state = ARB_FIRST, old_count = 0;
     uint32_t old_hash[2] = { 0, 0 };
     double old_jn[2] = { 0, 0 }, old_jt[2] = { 0, 0 };
@@ -511,93 +354,108 @@ __device__ int arbiter_update(EnvRef e, int sa, int sb, int ia, int ib, const Ma
         uint32_t hh = (uint32_t)AIF(e, slot, AI_HASH);
         old_hash[0] = hh & 0xffff; old_hash[1] = hh >> 16;
         MG_NOUNROLL
-        for (int q = 0; q < old_count; q++) { old_jn[q] = ACF(e, slot, q, AC_JN); old_jt[q] = ACF(e, slot, q, AC_JT); }
+        for (int k = 0; k < old_count; k++) { old_jn[k] = ACF(e, slot, k, AC_JN); old_jt[k] = ACF(e, slot, k, AC_JT); }
     }
+    const bool pooled = q < e.apn;
+    double *wp = pooled ? e.ap + (size_t)q * A_NF : &AF(e, slot, 0);
     vec2 pa = body_p(e, ba), pb = body_p(e, bb);
     MG_NOUNROLL
     for (int k = 0; k < m.count; k++) {
         vec2 r1 = vsub(m.p1[k], pa), r2 = vsub(m.p2[k], pb);
         double jn = 0.0, jt = 0.0;
         MG_NOUNROLL
-        for (int q = 0; q < old_count; q++)
-            if (m.hash[k] == old_hash[q]) { jn = old_jn[q]; jt = old_jt[q]; }
-        ACF(e, slot, k, AC_R1X) = r1.x; ACF(e, slot, k, AC_R1Y) = r1.y;
-        ACF(e, slot, k, AC_R2X) = r2.x; ACF(e, slot, k, AC_R2Y) = r2.y;
-        ACF(e, slot, k, AC_JN) = jn; ACF(e, slot, k, AC_JT) = jt;
+        for (int o = 0; o < old_count; o++)
+            if (m.hash[k] == old_hash[o]) { jn = old_jn[o]; jt = old_jt[o]; }
+        double *c = wp + A_CON0 + k * AC_NF;
+        c[AC_R1X] = r1.x; c[AC_R1Y] = r1.y; c[AC_R2X] = r2.x; c[AC_R2Y] = r2.y;
+        c[AC_JN] = jn; c[AC_JT] = jt;
     }
-    AF(e, slot, A_NX) = m.n.x; AF(e, slot, A_NY) = m.n.y;
-    AF(e, slot, A_U) = shape_friction(ia & 255) * shape_friction(ib & 255);
+    wp[A_NX] = m.n.x; wp[A_NY] = m.n.y;
+    wp[A_U] = shape_friction(ia & 255) * shape_friction(ib & 255);
     if (state == ARB_CACHED) state = ARB_FIRST;
     AIF(e, slot, AI_KEY) = key | (ba << 16) | (bb << 24);
     AIF(e, slot, AI_STAMP) = stamp;
     AIF(e, slot, AI_FLAGS) = state | (m.count << 8) | (1 << 16);
     AIF(e, slot, AI_HASH) = (int)(m.hash[0] | (m.count > 1 ? m.hash[1] << 16 : 0u));
+    if (pooled) e.ainfo[q] = ba | (bb << 8) | (m.count << 16) | (state << 24);
     return slot;
 }
 
-__device__ void arb_prestep(EnvRef e, int s, double slop, double bias_c)
+/* after the last iteration of a sub-step: jn / jt of the pooled arbiters go back to their cache slots (warm start) */
+__device__ __forceinline__ void arb_pool_writeback(EnvRef e, const unsigned char *order, int n_live)
+{
+    const int n = n_live < e.apn ? n_live : e.apn;
+    MG_NOUNROLL
+    for (int q = 0; q < n; q++) {
+        const int s = order[q], count = (e.ainfo[q] >> 16) & 255;
+        const double *c = e.ap + (size_t)q * A_NF + A_CON0;
+        MG_NOUNROLL
+        for (int k = 0; k < count; k++) { ACF(e, s, k, AC_JN) = c[k * AC_NF + AC_JN]; ACF(e, s, k, AC_JT) = c[k * AC_NF + AC_JT]; }
+    }
+}
+
+__device__ void arb_prestep(EnvRef e, const unsigned char *order, int q, double slop, double bias_c)
 {
     const double dt = MG_DT;
-    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
-    int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
-    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    const ArbRef r = arb_ref(e, order, q);
+    const int a = r.a, b = r.b;
+    vec2 n = V(APF(r, A_NX), APF(r, A_NY));
     vec2 body_delta = vsub(body_p(e, b), body_p(e, a));
     MG_NOUNROLL
-    for (int k = 0; k < count; k++) {
-        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
-        ACF(e, s, k, AC_NMASS) = 1.0 / k_scalar(e, a, b, r1, r2, n);
-        ACF(e, s, k, AC_TMASS) = 1.0 / k_scalar(e, a, b, r1, r2, vperp(n));
+    for (int k = 0; k < r.count; k++) {
+        vec2 r1 = V(APC(r, k, AC_R1X), APC(r, k, AC_R1Y)), r2 = V(APC(r, k, AC_R2X), APC(r, k, AC_R2Y));
+        APC(r, k, AC_NMASS) = 1.0 / k_scalar(e, a, b, r1, r2, n);
+        APC(r, k, AC_TMASS) = 1.0 / k_scalar(e, a, b, r1, r2, vperp(n));
         double dist = vdot(vadd(vsub(r2, r1), body_delta), n);
-        ACF(e, s, k, AC_BIAS) = -bias_c * cp_min(0.0, dist + slop) / dt;
-        ACF(e, s, k, AC_JBIAS) = 0.0;
+        APC(r, k, AC_BIAS) = -bias_c * cp_min(0.0, dist + slop) / dt;
+        APC(r, k, AC_JBIAS) = 0.0;
         /* bounce = normal_relative_velocity * e with e = 0 for every shape */
     }
 }
 
-__device__ void arb_apply_cached(EnvRef e, int s, double dt_coef)
+__device__ void arb_apply_cached(EnvRef e, const unsigned char *order, int q, double dt_coef)
 {
-    int fl = AIF(e, s, AI_FLAGS);
-    if ((fl & 255) == ARB_FIRST) return;
-    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
-    int count = (fl >> 8) & 255;
-    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
+    const ArbRef r = arb_ref(e, order, q);
+    if (r.state == ARB_FIRST) return;
+    const int a = r.a, b = r.b;
+    vec2 n = V(APF(r, A_NX), APF(r, A_NY));
     MG_NOUNROLL
-    for (int k = 0; k < count; k++) {
-        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
-        vec2 j = vrot(n, V(ACF(e, s, k, AC_JN), ACF(e, s, k, AC_JT)));
+    for (int k = 0; k < r.count; k++) {
+        vec2 r1 = V(APC(r, k, AC_R1X), APC(r, k, AC_R1Y)), r2 = V(APC(r, k, AC_R2X), APC(r, k, AC_R2Y));
+        vec2 j = vrot(n, V(APC(r, k, AC_JN), APC(r, k, AC_JT)));
         apply_impulses(e, a, b, r1, r2, vmul(j, dt_coef));
     }
 }
 
-__device__ void arb_apply_impulse(EnvRef e, int s)
+__device__ void arb_apply_impulse(EnvRef e, const unsigned char *order, int q)
 {
-    int key = AIF(e, s, AI_KEY), a = (key >> 16) & 255, b = (key >> 24) & 255;
-    int count = (AIF(e, s, AI_FLAGS) >> 8) & 255;
-    vec2 n = V(AF(e, s, A_NX), AF(e, s, A_NY));
-    double friction = AF(e, s, A_U);
+    const ArbRef r = arb_ref(e, order, q);
+    const int a = r.a, b = r.b;
+    vec2 n = V(APF(r, A_NX), APF(r, A_NY));
+    double friction = APF(r, A_U);
     MG_NOUNROLL
-    for (int k = 0; k < count; k++) {
-        double n_mass = ACF(e, s, k, AC_NMASS);
-        vec2 r1 = V(ACF(e, s, k, AC_R1X), ACF(e, s, k, AC_R1Y)), r2 = V(ACF(e, s, k, AC_R2X), ACF(e, s, k, AC_R2Y));
+    for (int k = 0; k < r.count; k++) {
+        double n_mass = APC(r, k, AC_NMASS);
+        vec2 r1 = V(APC(r, k, AC_R1X), APC(r, k, AC_R1Y)), r2 = V(APC(r, k, AC_R2X), APC(r, k, AC_R2Y));
         vec2 vb1 = vadd(V(BF(e, a, B_VBX), BF(e, a, B_VBY)), vmul(vperp(r1), BF(e, a, B_WB)));
         vec2 vb2 = vadd(V(BF(e, b, B_VBX), BF(e, b, B_VBY)), vmul(vperp(r2), BF(e, b, B_WB)));
         vec2 vr = relative_velocity(e, a, b, r1, r2);
         double vbn = vdot(vsub(vb2, vb1), n);
         double vrn = vdot(vr, n);
         double vrt = vdot(vr, vperp(n));
-        double jbn = (ACF(e, s, k, AC_BIAS) - vbn) * n_mass;
-        double jbn_old = ACF(e, s, k, AC_JBIAS);
+        double jbn = (APC(r, k, AC_BIAS) - vbn) * n_mass;
+        double jbn_old = APC(r, k, AC_JBIAS);
         double j_bias = cp_max(jbn_old + jbn, 0.0);
-        ACF(e, s, k, AC_JBIAS) = j_bias;
+        APC(r, k, AC_JBIAS) = j_bias;
         double jn = -(0.0 + vrn) * n_mass;
-        double jn_old = ACF(e, s, k, AC_JN);
+        double jn_old = APC(r, k, AC_JN);
         double jn_acc = cp_max(jn_old + jn, 0.0);
-        ACF(e, s, k, AC_JN) = jn_acc;
+        APC(r, k, AC_JN) = jn_acc;
         double jt_max = friction * jn_acc;
-        double jt = -vrt * ACF(e, s, k, AC_TMASS);
-        double jt_old = ACF(e, s, k, AC_JT);
+        double jt = -vrt * APC(r, k, AC_TMASS);
+        double jt_old = APC(r, k, AC_JT);
         double jt_acc = dclamp(jt_old + jt, -jt_max, jt_max);
-        ACF(e, s, k, AC_JT) = jt_acc;
+        APC(r, k, AC_JT) = jt_acc;
         vec2 jb = vmul(n, j_bias - jbn_old);
         apply_bias_impulse(e, a, vneg(jb), r1);
         apply_bias_impulse(e, b, jb, r2);
@@ -806,12 +664,43 @@ __device__ int coop_collide(const WShape *a, const WShape *b, Manifold *m, int g
 }
 
 
+/* ---- section timers (-DMG_SECTION_TIMERS, tools/section_timers.py): clock64 deltas of the phases of a CTA's step, taken
+ * on thread 0 (lane 0 of the warp that runs the serial halves), summed over the ten sub-steps.  Not in product builds. */
+#ifdef MG_SECTION_TIMERS
+#define MG_NTIMERS 16
+#define MG_TIMER_CTAS 8192
+__device__ long long mg_phys_timers[MG_TIMER_CTAS * MG_NTIMERS];
+__device__ __forceinline__ void tm_add(long long *tm, int k, long long &t)
+{
+    const long long now = clock64();
+    if (tm) tm[k] += now - t;
+    t = now;
+}
+#define TM_DECL(tm_) long long tm_t_ = clock64(); long long *tm_p_ = (tm_)
+#define TM_ADD(k_) tm_add(tm_p_, (k_), tm_t_)
+enum { TM_PARALLEL, TM_BARRIER, TM_SERIAL, TM_SPRING, TM_CACHED, TM_ARB, TM_BLOCKCON, TM_ROBOTCON, TM_TOTAL, TM_STAGE, TM_REGS,
+       TM_P_INTEG, TM_P_BB, TM_P_PAIRS, TM_P_PRESTEP };
+extern "C" int mg_debug_read_timers(long long *out_host, int n_ctas)
+{
+    if (n_ctas > MG_TIMER_CTAS) n_ctas = MG_TIMER_CTAS;
+    cudaDeviceSynchronize();
+    cudaError_t e = cudaMemcpyFromSymbol(out_host, mg_phys_timers, (size_t)n_ctas * MG_NTIMERS * sizeof(long long));
+    static long long zeros[MG_TIMER_CTAS * MG_NTIMERS];
+    cudaMemcpyToSymbol(mg_phys_timers, zeros, sizeof(zeros));
+    return e == cudaSuccess ? MG_NTIMERS : -1;
+}
+#else
+#define TM_DECL(tm_)
+#define TM_ADD(k_)
+#endif
+
 #define NARROW_SLOTS 1
 /* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
 struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
 
-__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, double *bbs)
+__device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, double *bbs, long long *tm = nullptr)
 {
+    TM_DECL(tm);
     const int gl = lane & (PHYS_LANES - 1);     /* lane within the env's group */
     const double dt = MG_DT;
     const int prev_stamp = IF(e, I_STAMP);
@@ -849,6 +738,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
     }
     __syncwarp(gmask);
 
+    TM_ADD(TM_P_INTEG);
     /* narrow phase over shape pairs in add order (i < j): for shape i the env's lanes take consecutive j,
      * run the bounding test and the narrow phase in parallel, then the hits update the arbiter cache one
      * after the other in j order -- the order a serial double loop discovers them in */
@@ -862,6 +752,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
         tpl_world_bb(T, info & 255, body_p(e, body), body_rot(e, body), bbs + 4 * s);
     }
     __syncwarp(gmask);
+    TM_ADD(TM_P_BB);
     MG_NOUNROLL
     for (int i = 0; i + 1 < (PHYS_DBG_SKIP == 3 || PHYS_DBG_SKIP == 4 ? 0 : ns); i++) {
         const int info_i = IF(e, I_SHAPE0 + i);
@@ -914,8 +805,8 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
                 if (PHYS_DBG_SKIP == 9) cnt = 0;
                 if (cnt) {
                     if (gl == 0) {
-                        int slot = swapped ? arbiter_update(e, js, i, info_s, info_i, *mf, stamp)
-                                           : arbiter_update(e, i, js, info_i, info_s, *mf, stamp);
+                        int slot = swapped ? arbiter_update(e, js, i, info_s, info_i, *mf, stamp, n_live)
+                                           : arbiter_update(e, i, js, info_i, info_s, *mf, stamp, n_live);
                         order[MG_NARB] = (unsigned char)(slot >= 0);
                         if (slot >= 0) order[n_live] = (unsigned char)slot;
                     }
@@ -927,16 +818,18 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
         }
     }
 
+    TM_ADD(TM_P_PAIRS);
     /* pre-step: arbiters and constraints only write their own fields ... */
     const double slop = 0.01;                       /* base_env.py:207 */
     const double bias_c = T->bias_coef_default;     /* 1 - collision_bias^dt */
     const int nc = IF(e, I_NCON);
     MG_NOUNROLL
-    for (int q = gl; q < n_live; q += PHYS_LANES) arb_prestep(e, order[q], slop, bias_c);
+    for (int q = gl; q < n_live; q += PHYS_LANES) arb_prestep(e, order, q, slop, bias_c);
     MG_NOUNROLL
     for (int c = gl; c < (PHYS_DBG_SKIP == 5 ? 0 : nc); c += PHYS_LANES)
         if ((IF(e, I_CON0 + c) & 255) != CON_SPRING) con_prestep(e, c);
     __syncwarp(gmask);
+    TM_ADD(TM_P_PRESTEP);
     return PHYS_DBG_SKIP == 7 ? 0 : n_live;
 }
 
@@ -1046,6 +939,41 @@ __device__ __forceinline__ void robot_constraints_pass(BodyV (&r)[MG_RB_COUNT], 
     reg_motor<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF);
 }
 
+/* con_apply_cached for the robot's ten constraints on the register copies (same formulas, operation for operation) */
+template <int A, int B>
+__device__ __forceinline__ void reg_cached_pivot(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)
+{
+    const vec2 j = vmul(V(cf[C_JX], cf[C_JY]), dt_coef);
+    reg_apply_impulse<A>(r, vneg(j), V(cf[C_R1X], cf[C_R1Y]));
+    reg_apply_impulse<B>(r, j, V(cf[C_R2X], cf[C_R2Y]));
+}
+template <int A, int B>
+__device__ __forceinline__ void reg_cached_gear(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)
+{
+    const double j = cf[C_JX] * dt_coef;
+    r[A].w = r[A].w - j * r[A].iinv * (1.0 / cf[C_P1]);
+    r[B].w = r[B].w + j * r[B].iinv;
+}
+template <int A, int B>
+__device__ __forceinline__ void reg_cached_scalar(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)   /* limit, motor */
+{
+    const double j = cf[C_JX] * dt_coef;
+    r[A].w = r[A].w - j * r[A].iinv;
+    r[B].w = r[B].w + j * r[B].iinv;
+}
+__device__ __forceinline__ void robot_cached_pass(BodyV (&r)[MG_RB_COUNT], const double *cf0, double dt_coef)
+{
+    reg_cached_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 0 * C_NF, dt_coef);
+    reg_cached_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 1 * C_NF, dt_coef);
+    /* 2, 3: damped rotary springs have no cached impulse */
+    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 4 * C_NF, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 5 * C_NF, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 6 * C_NF, dt_coef);
+    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 7 * C_NF, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 8 * C_NF, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF, dt_coef);
+}
+
 /* one sequential-impulse pass over the floor-friction pairs c_lo, c_lo + 2, .. < c_hi of the blocks (PivotJoint then
  * GearJoint between the static body and the block, Shape.setup, entities.py:700-708) with the same register
  * formulas.  The static body has zero inverse mass and inertia: every impulse leaves its velocity at +0.0, so it is
@@ -1068,8 +996,8 @@ __device__ __forceinline__ void block_constraints_pass(EnvRef e, int c_lo, int c
 
 __device__ __forceinline__ void robot_regs_load(EnvRef e, BodyV (&r)[MG_RB_COUNT])
 {
+    /* fully unrolled: a rolled loop indexes r[] dynamically, which puts the whole array into local memory */
 #pragma unroll
-    MG_NOUNROLL
     for (int k = 0; k < MG_RB_COUNT; k++) {
         const int b = MG_BODY_ROBOT + k;
         r[k].vx = BF(e, b, B_VX); r[k].vy = BF(e, b, B_VY); r[k].w = BF(e, b, B_W);
@@ -1079,7 +1007,6 @@ __device__ __forceinline__ void robot_regs_load(EnvRef e, BodyV (&r)[MG_RB_COUNT
 __device__ __forceinline__ void robot_regs_store(EnvRef e, const BodyV (&r)[MG_RB_COUNT])
 {
 #pragma unroll
-    MG_NOUNROLL
     for (int k = 0; k < MG_RB_COUNT; k++) {
         const int b = MG_BODY_ROBOT + k;
         BF(e, b, B_VX) = r[k].vx; BF(e, b, B_VY) = r[k].vy; BF(e, b, B_W) = r[k].w;
@@ -1090,8 +1017,9 @@ __device__ __forceinline__ void robot_regs_store(EnvRef e, const BodyV (&r)[MG_R
  * impulses and the sequential-impulse iterations.  The step kernel runs this for all envs of a CTA in
  * neighbouring lanes of one warp, so that the serial chains of several envs share their instruction issue. */
 template <bool BLOCK_REG>
-__device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_live)
+__device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_live, long long *tm = nullptr)
 {
+    TM_DECL(tm);
     const int nc = IF(e, I_NCON);
     /* cpDampedRotarySpring's pre-step applies the spring torque to both bodies: in add order.  No other
      * pre-step reads angular velocity, so running these after the parallel ones changes nothing. */
@@ -1101,12 +1029,14 @@ __device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_li
 
     /* cpBodyUpdateVelocity: gravity 0, damping 1, no forces -> identity */
 
+    TM_ADD(TM_SPRING);
     double dt_coef = IF(e, I_STEPPED) ? 1.0 : 0.0;  /* prev_dt == 0 ? 0 : dt / prev_dt */
     IF(e, I_STEPPED) = 1;
     MG_NOUNROLL
-    for (int q = 0; q < n_live; q++) arb_apply_cached(e, order[q], dt_coef);
+    for (int q = 0; q < n_live; q++) arb_apply_cached(e, order, q, dt_coef);
     MG_NOUNROLL
     for (int c = 0; c < nc; c++) con_apply_cached(e, c, dt_coef);
+    TM_ADD(TM_CACHED);
 
 #if PHYS_REGSOLVER
     /* constraints in add order: the robot's ten sit at c_robot, the blocks' pairs before or after them
@@ -1115,37 +1045,164 @@ __device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_li
     double *cf_robot = e.dc + (size_t)c_robot * C_NF;
     BodyV r[MG_RB_COUNT];
     robot_regs_load(e, r);
+    TM_ADD(TM_REGS);
     MG_NOUNROLL
     for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
         if (n_live) {
             /* contacts may involve any body: give them the current velocities and take theirs back */
             robot_regs_store(e, r);
             MG_NOUNROLL
-            for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order[q]);
+            for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order, q);
             robot_regs_load(e, r);
         }
+        TM_ADD(TM_ARB);
         if (BLOCK_REG) block_constraints_pass(e, 0, c_robot);
         else {
             MG_NOUNROLL
             for (int c = 0; c < c_robot; c++) con_apply_impulse(e, c);
         }
+        TM_ADD(TM_BLOCKCON);
         robot_constraints_pass(r, cf_robot);
+        TM_ADD(TM_ROBOTCON);
         if (BLOCK_REG) block_constraints_pass(e, c_robot + 10, nc);
         else {
             MG_NOUNROLL
             for (int c = c_robot + 10; c < nc; c++) con_apply_impulse(e, c);
         }
+        TM_ADD(TM_BLOCKCON);
     }
     robot_regs_store(e, r);
+    TM_ADD(TM_REGS);
+    arb_pool_writeback(e, order, n_live);
 #else
     MG_NOUNROLL
     for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
         MG_NOUNROLL
-        for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order[q]);
+        for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order, q);
         MG_NOUNROLL
         for (int c = 0; c < nc; c++) con_apply_impulse(e, c);
     }
 #endif
+}
+
+#ifndef PHYS_HELPERS
+#define PHYS_HELPERS 1     /* the blocks' floor-friction pairs run on the other warps, concurrently with the robot chain on warp 0 */
+#endif
+
+/* con_apply_cached for the floor-friction pair of one block (PivotJoint c, GearJoint c + 1 between the static body and
+ * block body b, Shape.setup, entities.py:700-708), block side only: the static body has zero inverse mass and inertia,
+ * so every impulse leaves its velocity at +0.0 */
+__device__ __forceinline__ void block_pair_cached(EnvRef e, int c, int b, double dt_coef)
+{
+    const double *cf = e.dc + (size_t)c * C_NF;
+    const double minv = BF(e, b, B_MINV), iinv = BF(e, b, B_IINV);
+    const vec2 j = vmul(V(cf[C_JX], cf[C_JY]), dt_coef);
+    const vec2 r2 = V(cf[C_R2X], cf[C_R2Y]);
+    BF(e, b, B_VX) = BF(e, b, B_VX) + j.x * minv;
+    BF(e, b, B_VY) = BF(e, b, B_VY) + j.y * minv;
+    double w = BF(e, b, B_W) + iinv * vcross(r2, j);
+    const double jg = cf[C_NF + C_JX] * dt_coef;
+    BF(e, b, B_W) = w + jg * iinv;
+}
+
+/* one sequential-impulse application of that pair: block_constraints_pass for a single block */
+__device__ __forceinline__ void block_pair_pass(EnvRef e, int c, int b)
+{
+    BodyV r[2];
+    r[0].vx = BF(e, 0, B_VX); r[0].vy = BF(e, 0, B_VY); r[0].w = BF(e, 0, B_W);
+    r[0].minv = BF(e, 0, B_MINV); r[0].iinv = BF(e, 0, B_IINV);
+    r[1].vx = BF(e, b, B_VX); r[1].vy = BF(e, b, B_VY); r[1].w = BF(e, b, B_W);
+    r[1].minv = BF(e, b, B_MINV); r[1].iinv = BF(e, b, B_IINV);
+    reg_pivot<0, 1>(r, e.dc + (size_t)c * C_NF);
+    reg_gear<0, 1>(r, e.dc + (size_t)(c + 1) * C_NF);
+    BF(e, b, B_VX) = r[1].vx; BF(e, b, B_VY) = r[1].vy; BF(e, b, B_W) = r[1].w;
+}
+
+/* The order-dependent rest of cpSpaceStep for all envs of a CTA, run by the whole CTA.
+ * Constraints that share no dynamic body commute exactly (each reads and writes only its own bodies' velocities and its
+ * own accumulators), and in these scenes the constraint graph is a star: the robot's ten constraints touch only the six
+ * robot bodies, and every block has one PivotJoint + GearJoint pair to the static body.  So the robot chains of the
+ * CTA's envs run side by side in warp 0 (lane k = env k, straight-line register code as before) while each block's pair
+ * runs on its own lane of the other warps (lane = (env, block)); every body still sees its own updates in Chipmunk's
+ * order.  Contacts can couple any two bodies, so they stay one ordered chain per env on warp 0, fenced from the
+ * constraint passes by CTA barriers -- only in CTAs where some env has a live contact (`any_live`, CTA-uniform). */
+/* The two roles are separate out-of-line functions so that each gets its own register allocation (the robot chain
+ * keeps six bodies' velocities and masses in registers through all ten iterations: inlined into the kernel it spilled
+ * inside the constraint pass).  Both pass the same CTA barriers the same number of times (warp-uniform roles). */
+/* (The env's shared-memory copy is addressed from the kernel's shared array inside the functions, not through pointer
+ * arguments: behind a call boundary pointer arguments are generic addresses, and every body / constraint access of the
+ * chain would become a generic load instead of an LDS.) */
+struct PhysSmemFixed;
+__device__ __forceinline__ EnvRef smem_env_ref(int k, int envs, int max_blocks, int pool_n, double *da, int *ia);
+__device__ __forceinline__ const unsigned char *smem_env_order(int k, int envs, int max_blocks, int pool_n);
+
+template <int ENVS>
+__device__ __noinline__ void solve_lead(const bool solver, const int k, const int max_blocks, const int pool_n, double *da, int *ia,
+                                        const int any_live, long long *tm)
+{
+    TM_DECL(tm);
+    const EnvRef es = smem_env_ref(k, ENVS, max_blocks, pool_n, da, ia);
+    const unsigned char *order_s = smem_env_order(k, ENVS, max_blocks, pool_n);
+    int n_live = 0, c_robot = 0;
+    double dt_coef = 0.0;
+    BodyV r[MG_RB_COUNT];
+    if (solver) {
+        n_live = order_s[MG_NARB + 1];
+        c_robot = IF(es, I_ROBOT_FIRST) ? 0 : IF(es, I_NCON) - 10;
+        /* cpDampedRotarySpring's pre-step applies the spring torque to both bodies: the robot's two springs, in add
+         * order.  No other pre-step reads angular velocity, so running these after the parallel ones changes nothing. */
+        con_prestep(es, c_robot + 2);
+        con_prestep(es, c_robot + 3);
+        TM_ADD(TM_SPRING);
+        /* cpBodyUpdateVelocity: gravity 0, damping 1, no forces -> identity */
+        dt_coef = IF(es, I_STEPPED) ? 1.0 : 0.0;     /* prev_dt == 0 ? 0 : dt / prev_dt */
+        MG_NOUNROLL
+        for (int q = 0; q < n_live; q++) arb_apply_cached(es, order_s, q, dt_coef);
+    }
+    if (any_live) __syncthreads();
+    double *cf_robot = es.dc + (size_t)c_robot * C_NF;
+    if (solver) {
+        robot_regs_load(es, r);
+        robot_cached_pass(r, cf_robot, dt_coef);
+    }
+    TM_ADD(TM_CACHED);
+    if (any_live) __syncthreads();
+    MG_NOUNROLL
+    for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
+        if (any_live) {
+            if (n_live) {
+                /* contacts may involve any body: give them the current velocities and take theirs back */
+                robot_regs_store(es, r);
+                MG_NOUNROLL
+                for (int q = 0; q < n_live; q++) arb_apply_impulse(es, order_s, q);
+                robot_regs_load(es, r);
+            }
+            __syncthreads();
+            TM_ADD(TM_ARB);
+        }
+        if (solver) robot_constraints_pass(r, cf_robot);
+        TM_ADD(TM_ROBOTCON);
+        if (any_live) { __syncthreads(); TM_ADD(TM_BLOCKCON); }
+    }
+    if (solver) { robot_regs_store(es, r); arb_pool_writeback(es, order_s, n_live); }
+    TM_ADD(TM_REGS);
+}
+
+template <int ENVS>
+__device__ __noinline__ void solve_helper(const bool helper, const int k, const int hb, const int max_blocks, const int pool_n, const int any_live)
+{
+    const EnvRef eh = smem_env_ref(k, ENVS, max_blocks, pool_n, nullptr, nullptr);
+    if (any_live) __syncthreads();
+    const int hc = helper ? (IF(eh, I_ROBOT_FIRST) ? 10 : 0) + 2 * hb : 0;
+    const int hbody = MG_BODY_BLOCK0 + hb;
+    if (helper) block_pair_cached(eh, hc, hbody, IF(eh, I_STEPPED) ? 1.0 : 0.0);
+    if (any_live) __syncthreads();
+    MG_NOUNROLL
+    for (int it = 0; it < 10; it++) {
+        if (any_live) __syncthreads();
+        if (helper) block_pair_pass(eh, hc, hbody);
+        if (any_live) __syncthreads();
+    }
 }
 
 /* ------------------------------------------------------------------ scores (magical/benchmarks/*.py score_on_end_of_traj) */
@@ -1429,28 +1486,49 @@ __device__ __noinline__ double env_debug_reward(EnvRef e)
 struct PhysSmemFixed {
     int i[(I_ARB0 + 3) & ~3];             /* counters, block / goal / constraint / shape infos */
     unsigned char order[MG_NARB + 8];     /* live arbiter slots in discovery order (+ flag bytes) */
+    int ainfo[MG_ARB_POOL];               /* bodies / count / state of the pooled live arbiters */
     NarrowScratch narrow;                 /* the pair of shapes in the narrow phase and their manifold */
 };
 #define PHYS_TABLE_BYTES ((int)((offsetof(MgTables, dl_off) + 15) & ~15))
 
 /* shapes of the largest env: robot circle, 4 finger quads, 4 walls, and up to MG_STAR_PIECES per block */
 __host__ __device__ inline int phys_max_shapes(int max_blocks) { return 4 + 5 + max_blocks * MG_STAR_PIECES; }
-__host__ __device__ inline int phys_smem_doubles(int max_blocks)
+__host__ __device__ inline int phys_smem_doubles(int max_blocks, int pool_n)
 {
     /* stride = 1 (mod 16) doubles: the solver lanes of neighbouring envs read the same field of their own
      * env at the same time, and this keeps those reads on different shared-memory banks */
-    int n = (1 + MG_RB_COUNT + max_blocks) * B_NF + (10 + 2 * max_blocks) * C_NF + 4 * phys_max_shapes(max_blocks);
+    int n = (1 + MG_RB_COUNT + max_blocks) * B_NF + (10 + 2 * max_blocks) * C_NF + 4 * phys_max_shapes(max_blocks) + pool_n * A_NF;
     return ((n + 15) & ~15) + 1;
+}
+
+/* env k of the CTA in the kernel's dynamic shared memory: [ tables | ENVS x nd doubles | ENVS x PhysSmemFixed ] */
+extern __shared__ __align__(16) unsigned char phys_smem_raw[];
+__device__ __forceinline__ EnvRef smem_env_ref(int k, int envs, int max_blocks, int pool_n, double *da, int *ia)
+{
+    const int nd = phys_smem_doubles(max_blocks, pool_n), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
+    const int pool_off = con_off + (10 + 2 * max_blocks) * C_NF + 4 * phys_max_shapes(max_blocks);
+    double *smd = (double *)(phys_smem_raw + PHYS_TABLE_BYTES);
+    PhysSmemFixed *sm = (PhysSmemFixed *)(smd + (size_t)envs * nd);
+    EnvRef e;
+    e.d = smd + (size_t)k * nd; e.dc = e.d + con_off; e.i = sm[k].i; e.da = da; e.ia = ia;
+    e.ap = e.d + pool_off; e.ainfo = sm[k].ainfo; e.apn = pool_n;
+    return e;
+}
+__device__ __forceinline__ const unsigned char *smem_env_order(int k, int envs, int max_blocks, int pool_n)
+{
+    const int nd = phys_smem_doubles(max_blocks, pool_n);
+    double *smd = (double *)(phys_smem_raw + PHYS_TABLE_BYTES);
+    return ((PhysSmemFixed *)(smd + (size_t)envs * nd))[k].order;
 }
 
 template <int PHYS_THREADS_T, bool BLOCK_REG, bool PERM>
 __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
-                                                                uint8_t *done_out, float *score_out, int max_blocks)
+                                                                uint8_t *done_out, float *score_out, int max_blocks, int pool_n)
 {
-    extern __shared__ __align__(16) unsigned char phys_smem_raw[];
     constexpr int ENVS = PHYS_THREADS_T / PHYS_LANES;     /* envs per CTA; lanes 0..ENVS-1 of warp 0 run their serial halves */
-    const int nd = phys_smem_doubles(max_blocks), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
+    const int nd = phys_smem_doubles(max_blocks, pool_n), con_off = (1 + MG_RB_COUNT + max_blocks) * B_NF;
     const int bb_off = con_off + (10 + 2 * max_blocks) * C_NF;     /* world boxes of the env's shapes, 4 doubles each */
+    const int pool_off = bb_off + 4 * phys_max_shapes(max_blocks); /* working storage of the first MG_ARB_POOL live arbiters */
     /* the collision half of the tables (templates, walls, constants) in shared memory: with the env state
      * resident there is little L1 left, and every table read from HBM/L2 is a ~700-cycle stall on a serial path */
     {
@@ -1467,6 +1545,13 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     const bool active = env0 + grp < S.num_envs;   /* idle groups of the last CTA still meet the barriers */
     const int env = PERM ? S.perm[active ? env0 + grp : env0] : (active ? env0 + grp : env0);
     const MgTables *T = (const MgTables *)phys_smem_raw;   /* only the fields before dl_off are valid */
+#ifdef MG_SECTION_TIMERS
+    long long *tm_cta = threadIdx.x == 0 && blockIdx.x < MG_TIMER_CTAS ? mg_phys_timers + (size_t)blockIdx.x * MG_NTIMERS : nullptr;
+    const long long tm_start = clock64();
+#else
+    long long *tm_cta = nullptr;
+#endif
+    TM_DECL(tm_cta);
     const EnvRef g = env_ref(S.dstate, S.istate, env);
     PhysSmemFixed *W = &sm[grp];
     __syncthreads();
@@ -1484,6 +1569,7 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     }
     EnvRef e;
     e.d = Wd; e.dc = Wd + con_off; e.i = W->i; e.da = g.da; e.ia = g.ia;
+    e.ap = Wd + pool_off; e.ainfo = W->ainfo; e.apn = pool_n;
 #if PHYS_BARRIER
     /* lane k of warp 0 runs the serial half of the step for env k of this CTA */
     const bool solver = threadIdx.x < ENVS && env0 + lane < S.num_envs;
@@ -1491,7 +1577,17 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     if (solver) {
         const EnvRef gs = env_ref(S.dstate, S.istate, PERM ? S.perm[env0 + lane] : env0 + lane);
         es.d = smd + (size_t)lane * nd; es.dc = es.d + con_off; es.i = sm[lane].i; es.da = gs.da; es.ia = gs.ia;
+        es.ap = es.d + pool_off; es.ainfo = sm[lane].ainfo; es.apn = pool_n;
     }
+#if PHYS_HELPERS
+    /* the other warps: lane = (env k of the CTA, block hb of that env) runs that block's floor-friction pair */
+    constexpr int SLOTS_PER_WARP = 32 / ENVS;
+    static_assert((PHYS_THREADS_T / 32 - 1) * SLOTS_PER_WARP >= MG_MAX_BLOCKS, "a helper lane per block");
+    const int hk = lane % ENVS, hb = (threadIdx.x / 32 - 1) * SLOTS_PER_WARP + lane / ENVS;
+    EnvRef eh = e;
+    eh.d = smd + (size_t)hk * nd; eh.dc = eh.d + con_off; eh.i = sm[hk].i;
+    bool helper = false;          /* known once the env is staged (block count) */
+#endif
 #endif
     /* ACTION_ID_TO_FLAGS: id = ud + 3 * lr + 9 * grip (entities.py:148-190); Robot.set_action (:435-453) */
     int action = active ? actions[env] : 0;
@@ -1505,9 +1601,15 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     if (lr == 2) rel_turn_angle -= 1.5;
     double target_finger_angle = grip == 0 ? M_PI / 8 : -0.0;
 
+#if PHYS_BARRIER && PHYS_HELPERS
+    __syncthreads();              /* every env of the CTA is staged: the helper lanes read another group's counters */
+    helper = threadIdx.x >= 32 && env0 + hk < S.num_envs && hb < IF(eh, I_NBLOCKS);
+#endif
+    TM_ADD(TM_STAGE);
     const int rb = MG_BODY_ROBOT;
     const int motor_l = active ? (IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6) : 0;  /* robot constraints 0..9: motors are 6 and 9 */
     for (int sub = 0; sub < 10; sub++) {
+        int n_live_sub = 0;
         if (active) {
             if (gl == 0) {
                 /* Robot.update (entities.py:455-476) */
@@ -1525,20 +1627,34 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
             }
             __syncwarp(gmask);
 #if PHYS_DBG_SKIP != 2
-            int n_live = space_step_parallel(e, T, lane, gmask, W->order, &W->narrow, Wd + bb_off);
+            int n_live = space_step_parallel(e, T, lane, gmask, W->order, &W->narrow, Wd + bb_off, tm_cta);
 #else
             int n_live = 0;
 #endif
             if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
+            n_live_sub = n_live;
         }
 #if PHYS_BARRIER
         /* the order-dependent halves of all envs of the CTA in neighbouring lanes of warp 0: their serial
          * chains then cost one instruction stream instead of ENVS */
+        TM_ADD(TM_PARALLEL);
+#if PHYS_HELPERS
+        const int any_live = __syncthreads_or(n_live_sub != 0);
+        TM_ADD(TM_BARRIER);
+        if (threadIdx.x < 32) solve_lead<ENVS>(solver, lane & (ENVS - 1), max_blocks, pool_n, es.da, es.ia, any_live, tm_cta);
+        else solve_helper<ENVS>(helper, hk, hb, max_blocks, pool_n, any_live);
+        TM_ADD(TM_SERIAL);
         __syncthreads();
+        if (active && gl == 0) IF(e, I_STEPPED) = 1;      /* after the barrier: the helper lanes read it for dt_coef */
+#else
+        __syncthreads();
+        TM_ADD(TM_BARRIER);
 #if PHYS_DBG_SKIP != 1
-        if (solver) space_step_serial<BLOCK_REG>(es, sm[lane].order, sm[lane].order[MG_NARB + 1]);
+        if (solver) space_step_serial<BLOCK_REG>(es, sm[lane].order, sm[lane].order[MG_NARB + 1], tm_cta);
 #endif
+        TM_ADD(TM_SERIAL);
         __syncthreads();
+#endif
 #else
         if (active) {
             /* the order-dependent half on the group's first lane; groups never wait for each other */
@@ -1547,6 +1663,9 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
         }
 #endif
     }
+#ifdef MG_SECTION_TIMERS
+    if (tm_cta) tm_cta[TM_TOTAL] += clock64() - tm_start;
+#endif
     if (!active) return;
 
     const int steps = IF(e, I_EPISODE_STEPS) + 1;
@@ -1655,6 +1774,11 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
     if (n <= 0) return;
     mg_init_kernel<<<(n + 31) / 32, 32, 0, st>>>(S, scenes_dev, env_ids_dev, n);
 }
+void mg_launch_mark_pending(const MgDeviceState &S, const int32_t *env_ids_dev, int n, cudaStream_t st)
+{
+    if (n <= 0) return;
+    mg_mark_pending_kernel<<<(n + 127) / 128, 128, 0, st>>>(S, env_ids_dev, n);
+}
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st)
 {
     /* the shared-memory opt-in is a per-device (per-context) function attribute: track it per CUDA ordinal */
@@ -1667,13 +1791,25 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
     if (max_blocks < 0) max_blocks = 0;
     if (max_blocks > MG_MAX_BLOCKS) max_blocks = MG_MAX_BLOCKS;
     /* 16 envs per CTA while two such CTAs fit one SM; larger scenes run 8 envs per CTA so that three (two
-     * at the largest block counts) stay resident instead of one */
-    const size_t per_env = (size_t)phys_smem_doubles(max_blocks) * sizeof(double) + sizeof(PhysSmemFixed);
+     * at the largest block counts) stay resident instead of one.  The shared-memory pool of live arbiters takes
+     * whatever is left: the largest size that keeps the CTA shape and the number of resident CTAs */
     const size_t smem_sm = 233472, smem_cta_reserved = 1024;
-    const bool wide = 2 * (PHYS_TABLE_BYTES + per_env * PHYS_ENVS + smem_cta_reserved) <= smem_sm;
+    auto per_env_bytes = [&](int pool) { return (size_t)phys_smem_doubles(max_blocks, pool) * sizeof(double) + sizeof(PhysSmemFixed); };
+    auto is_wide = [&](int pool) { return 2 * (PHYS_TABLE_BYTES + per_env_bytes(pool) * PHYS_ENVS + smem_cta_reserved) <= smem_sm; };
+    auto resident = [&](int pool) {
+        const int envs_ = is_wide(pool) ? PHYS_ENVS : PHYS_ENVS / 2;
+        const int by_smem = (int)(smem_sm / (PHYS_TABLE_BYTES + per_env_bytes(pool) * envs_ + smem_cta_reserved));
+        const int by_regs = 512 / (envs_ * PHYS_LANES);            /* __launch_bounds__ of the kernel */
+        return by_smem < by_regs ? by_smem : by_regs;
+    };
+    int pool_n = 0;
+    for (int p = MG_ARB_POOL; p > 0; p -= 2)
+        if (is_wide(p) == is_wide(0) && resident(p) >= resident(0)) { pool_n = p; break; }
+    const size_t per_env = per_env_bytes(pool_n);
+    const bool wide = is_wide(pool_n);
     const int envs = wide ? PHYS_ENVS : PHYS_ENVS / 2;
     const size_t smem = PHYS_TABLE_BYTES + per_env * envs;
-    const size_t smem_full = PHYS_TABLE_BYTES + per_env * PHYS_ENVS;
+    const size_t smem_full = PHYS_TABLE_BYTES + per_env_bytes(MG_ARB_POOL) * PHYS_ENVS;
     if (smem_full > attr_set) {
         const int a = (int)smem_full;
         cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
@@ -1688,14 +1824,19 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
     /* scenes with several blocks run the blocks' floor-friction pairs through the register formulas; with at most one
      * block the generic constraint path measured faster (0.476 vs 0.502 ms at 4096 MoveToCorner envs).  The PERM
      * instantiations take their envs through S.perm (mg_step in parts). */
-#define PHYS_LAUNCH(T_, R_, P_) mg_physics_kernel<T_, R_, P_><<<grid, T_, smem, st>>>(S, actions, reward, done, score, max_blocks)
+#define PHYS_LAUNCH(T_, R_, P_) mg_physics_kernel<T_, R_, P_><<<grid, T_, smem, st>>>(S, actions, reward, done, score, max_blocks, pool_n)
+#if PHYS_HELPERS
+    const bool block_reg = true;          /* the block pairs always run through the register formulas on their own lanes */
+#else
+    const bool block_reg = max_blocks > 1;
+#endif
     if (S.perm) {
         if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, true);
-        else if (max_blocks > 1) PHYS_LAUNCH(PHYS_THREADS, true, true);
+        else if (block_reg) PHYS_LAUNCH(PHYS_THREADS, true, true);
         else PHYS_LAUNCH(PHYS_THREADS, false, true);
     } else {
         if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, false);
-        else if (max_blocks > 1) PHYS_LAUNCH(PHYS_THREADS, true, false);
+        else if (block_reg) PHYS_LAUNCH(PHYS_THREADS, true, false);
         else PHYS_LAUNCH(PHYS_THREADS, false, false);
     }
 #undef PHYS_LAUNCH

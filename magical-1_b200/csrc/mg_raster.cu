@@ -20,10 +20,12 @@
  * of an integer DDA line after Cohen-Sutherland clipping with a float slope.
  */
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <mutex>
 #include "mg_state.cuh"
 #include "mg_kernels.h"
 #include "../../include/mg_trig.h"
+#include "mg_envref.cuh"
 
 #define RES MG_RES
 #ifndef BAND_ROWS
@@ -445,13 +447,22 @@ struct RenderArgs {
  * (Viewer.render -> Geom.render -> stack.apply_current_matrix, render.py:116-160, 373-392), transforms the
  * vertices in FP64 and truncates them the way pygame converts its float arguments to int.  The band
  * rasterisers then only see integers. */
-__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view, int env_begin, int env_end)
+__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view, int env_begin, int env_end, int apply_pending)
 {
     const MgTables *T = S.tables;
     const int lane = threadIdx.x & 31;
     const int slot = env_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (slot >= env_end) return;
     const int env = S.perm ? S.perm[slot] : slot;
+    /* a reset queued for this env (mg_queue_resets): this step's physics is done with the old episode (stream order),
+     * so the env is re-initialised here, right before the first frame of the new episode is drawn */
+    if (apply_pending && S.pending) {
+        const int p = S.pending[env];
+        if (p >= 0) {
+            if (lane == 0) { init_env(S, S.pending_scenes + p, env); S.pending[env] = -1; }
+            __syncwarp();
+        }
+    }
     const double *pose = S.poses + (size_t)env * MG_POSE_STRIDE;
     const double *rp = pose + MG_BODY_ROBOT * MG_POSE_NF;
     const aff cam = view == MG_VIEW_ALLO ? allo_camera() : ego_camera(rp[0], rp[1], rp[6], rp[7]);
@@ -630,12 +641,32 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
             __syncwarp();
             if (P.mode == 1) {
-                /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis */
+                /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis.
+                 * Edges whose rows (+1 for the shifted copy) miss the band are dropped first, so that a 100-gon that
+                 * spans three or four bands costs each of them only the batches of its own edges. */
+                uint8_t *edges = (uint8_t *)W->span_lo;            /* <= MG_CIRCLE_RES entries of the 384 bytes of span_* */
+                int n_edges = 0;
+                {
+                    const unsigned lt = (1u << lane) - 1;
+                    RNOUNROLL
+                    for (int i0 = 0; i0 < n; i0 += 32) {
+                        const int i = i0 + lane;
+                        bool ok = false;
+                        if (i < n) {
+                            const int ya = W->vy[i], yb = W->vy[i + 1];
+                            ok = max(ya, yb) + 1 >= y0 && min(ya, yb) < y0 + BAND_ROWS;
+                        }
+                        const unsigned m = __ballot_sync(FULL, ok);
+                        if (ok) edges[n_edges + __popc(m & lt)] = (uint8_t)i;
+                        n_edges += __popc(m);
+                    }
+                    __syncwarp();
+                }
                 RNOUNROLL
-                for (int job0 = 0; job0 < 2 * n; job0 += 32) {
+                for (int job0 = 0; job0 < 2 * n_edges; job0 += 32) {
                     const int job = job0 + lane;
-                    const bool has = job < 2 * n;
-                    const int i = has ? job >> 1 : 0, copy = job & 1;
+                    const bool has = job < 2 * n_edges;
+                    const int i = has ? edges[job >> 1] : 0, copy = job & 1;
                     int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
                     if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
                     draw_line_jobs(W->buf, y0, lane, has, x1, y1, x2, y2, P.outline);
@@ -695,20 +726,50 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
      * palette index (the vast majority) are a table look-up; the mixed ones are queued and summed in a
      * second, dense pass so that one mixed block does not drag its 31 neighbours through the slow path. */
     {
-        uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now */
+        uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now: MIXED_MAX entries fill both */
 #ifdef MG_TEST_MIXED_MAX
         const int MIXED_MAX = MG_TEST_MIXED_MAX;                   /* test builds: force the every-block fallback below */
 #else
         const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
+        static_assert(sizeof(uint16_t) * 4 * (MG_CIRCLE_RES + 4) <= sizeof(W->vx) + sizeof(W->vy) && offsetof(WarpSmem, vy) == offsetof(WarpSmem, vx) + sizeof(W->vx), "mixed-block queue = vx + vy");
+        static_assert(LO_ROWS * MG_LORES / 4 <= 3 * BAND_ROWS * (int)sizeof(int) && MG_CIRCLE_RES <= 3 * BAND_ROWS * (int)sizeof(int), "quad / edge lists fit span_*");
 #endif
         int n_mixed = 0;
         {
-            /* a lane takes four neighbouring blocks: four 16-byte loads in, three words (4 x RGB) out; quad
-             * q = lane + 32 it, 24 quads per block row */
+            /* Pass 1, a lane takes four neighbouring blocks (a quad: 16 x 4 pixels): four 16-byte loads in, three words
+             * (4 x RGB) out; quad q = lane + 32 it, 24 quads per block row.  Most quads are one colour (floor, background,
+             * the inside of a shape): those are one table look-up; the others are queued and done block by block in a
+             * dense second pass, so that a quad with an edge in it does not drag its 31 neighbours through the slow path. */
             const unsigned lt_mask = (1u << lane) - 1;
             uint32_t *lo_w = (uint32_t *)W->lo;
+            uint8_t *quads = (uint8_t *)W->span_lo;                /* span_* (384 bytes) are dead by now; <= 192 entries (the mixed-block queue fills vx AND vy) */
+            int n_quads = 0;
             RNOUNROLL
             for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads */
+                const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
+                const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
+                const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
+                const uint4 r2 = *(const uint4 *)(base + 2 * ROW_STRIDE), r3 = *(const uint4 *)(base + 3 * ROW_STRIDE);
+                const uint32_t a = r0.x;
+                const uint32_t diff = ((a ^ r0.y) | (a ^ r0.z) | (a ^ r0.w)) | ((a ^ r1.x) | (a ^ r1.y) | (a ^ r1.z) | (a ^ r1.w))
+                                      | ((a ^ r2.x) | (a ^ r2.y) | (a ^ r2.z) | (a ^ r2.w)) | ((a ^ r3.x) | (a ^ r3.y) | (a ^ r3.z) | (a ^ r3.w))
+                                      | (a ^ ((a & 255) * 0x01010101u));
+                const unsigned m = __ballot_sync(FULL, diff != 0);
+                if (diff) quads[n_quads + __popc(m & lt_mask)] = (uint8_t)q;
+                else {
+                    const uint32_t c = pal[a & 31];
+                    lo_w[3 * q] = c | c << 24;
+                    lo_w[3 * q + 1] = c >> 8 | c << 16;
+                    lo_w[3 * q + 2] = c >> 16 | c << 8;
+                }
+                n_quads += __popc(m);
+            }
+            __syncwarp();
+            /* Pass 2, the quads with more than one colour: per block, one-colour blocks by look-up, the mixed ones queued */
+            RNOUNROLL
+            for (int k0 = 0; k0 < n_quads; k0 += 32) {
+                const bool has = k0 + lane < n_quads;
+                const int q = has ? quads[k0 + lane] : 0;
                 const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
                 const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
                 const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
@@ -718,7 +779,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                 uint32_t rgb[4];
 #pragma unroll
                 for (int b = 0; b < 4; b++) {
-                    const bool mix = !(w0[b] == w1[b] && w0[b] == w2[b] && w0[b] == w3[b] && w0[b] == (w0[b] & 255) * 0x01010101u);
+                    const bool mix = has && !(w0[b] == w1[b] && w0[b] == w2[b] && w0[b] == w3[b] && w0[b] == (w0[b] & 255) * 0x01010101u);
                     rgb[b] = pal[w0[b] & 31];                /* right for a one-colour block; mixed ones are redone below */
                     const unsigned m = __ballot_sync(FULL, mix);
                     if (mix) {
@@ -727,9 +788,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
                     }
                     n_mixed += __popc(m);
                 }
-                lo_w[3 * q] = rgb[0] | rgb[1] << 24;
-                lo_w[3 * q + 1] = rgb[1] >> 8 | rgb[2] << 16;
-                lo_w[3 * q + 2] = rgb[2] >> 16 | rgb[3] << 8;
+                if (has) {
+                    lo_w[3 * q] = rgb[0] | rgb[1] << 24;
+                    lo_w[3 * q + 1] = rgb[1] >> 8 | rgb[2] << 16;
+                    lo_w[3 * q + 2] = rgb[2] >> 16 | rgb[3] << 8;
+                }
             }
         }
         __syncwarp();
@@ -860,16 +923,16 @@ __global__ void mg_clear_fresh_kernel(MgDeviceState S)
     if (env < S.num_envs) S.istate[mg_field_index(env, I_NF, I_FRESH)] = 0;
 }
 
-void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st)
+void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st, int apply_pending)
 {
     if (env_end <= env_begin) return;
-    mg_geometry_kernel<<<(env_end - env_begin + 3) / 4, 128, 0, st>>>(S, view, env_begin, env_end);
+    mg_geometry_kernel<<<(env_end - env_begin + 3) / 4, 128, 0, st>>>(S, view, env_begin, env_end, apply_pending);
 }
 
-static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st)
+static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st, int apply_pending = 0)
 {
     if (A.env_end <= A.env_begin) return;
-    mg_launch_geometry(S, A.view, A.env_begin, A.env_end, st);
+    mg_launch_geometry(S, A.view, A.env_begin, A.env_end, st, apply_pending);
     /* per-device function attribute (see mg_launch_physics) */
     static bool attr_set_dev[MG_MAX_DEVICES] = { false };
     static std::mutex attr_mu;
@@ -899,7 +962,7 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
 }
 
 void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgObsSpec *fused, const int *slots,
-                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st)
+                           uint8_t *obs, int env_begin, int env_end, cudaStream_t st, int apply_pending)
 {
     RenderArgs A;
     memset(&A, 0, sizeof(A));
@@ -911,7 +974,7 @@ void mg_launch_render_push(const MgDeviceState &S, int view, int slot, const MgO
             A.gslot[g] = (slots[fused->view[g]] - fused->age[g]) & (MG_MAX_RING - 1);
         }
     }
-    launch_render(S, A, st);
+    launch_render(S, A, st, apply_pending);
 }
 
 void mg_launch_render_out(const MgDeviceState &S, int view, int full_res, uint8_t *out, cudaStream_t st)

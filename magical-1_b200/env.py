@@ -9,6 +9,8 @@ and keeps the per-env episode counters.  torch is used for device memory and str
 """
 import collections
 import os
+import queue
+import threading
 import ctypes as C
 
 import numpy as np
@@ -34,6 +36,114 @@ PREPROC_SPECS = collections.OrderedDict([
 def _torch():
     import torch
     return torch
+
+
+class _SceneView:
+    """List-like view of the scene every env was last reset to.  The scenes live as raw mg_scene bytes
+    ([B, sizeof(mg_scene)] uint8) so that thousands of resets per step cost one vectorised copy; an item is
+    materialised as a ctypes Scene copy on access."""
+
+    def __init__(self, raw):
+        self._raw = raw
+
+    def __len__(self):
+        return self._raw.shape[0]
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[k] for k in range(*i.indices(len(self)))]
+        return L.Scene.from_buffer_copy(self._raw[int(i)].tobytes())
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
+class _ResetFeeder:
+    """Samples, on a host thread, the initial states of the episodes that will start on FUTURE steps while the GPU
+    runs the current ones.  Episode ends are known in advance (an env finishes when its step counter reaches its
+    horizon), so the thread walks the schedule ahead of the stepping loop: for every coming step with finishing envs
+    it draws those envs' next scenes from their own RandomState streams (native reset engine, reference draw order)
+    and queues them.  The streams therefore run ahead of the episodes; `cancel()` rolls every unconsumed draw back, so
+    whoever looks at the streams (reset(), seed(), rngs, set_state ...) sees them where a synchronous env would."""
+
+    CHUNK_ENVS = 512      # envs sampled per call of the native engine (it starts its threads per call)
+
+    def __init__(self, env, depth=16):
+        self.env = env
+        self.q = queue.Queue(maxsize=depth)
+        self.lock = threading.Lock()
+        self.items = []           # produced, not yet consumed: (step, ids, scenes_bytes, error, keys_before, pos_before)
+        self.stop = False
+        h = env._horizons
+        self.next_finish = env._abs_step + np.maximum(h - env._episode_steps, 1)
+        self.max_span = max(1, int(h.min()) - 1)     # an env appears at most once per chunk
+        self.thread = threading.Thread(target=self._run, daemon=True)
+        self.thread.start()
+
+    def _run(self):
+        env, H = self.env, self.env._horizons
+        nscene = C.sizeof(L.Scene)
+        while not self.stop:
+            # the next few steps that have finishing envs, up to CHUNK_ENVS envs, in one call of the engine
+            s0 = int(self.next_finish.min())
+            steps, ids_per_step, total = [], [], 0
+            s = s0
+            while s - s0 < self.max_span and total < self.CHUNK_ENVS and len(steps) < 8:
+                ids = np.nonzero(self.next_finish == s)[0]
+                if len(ids):
+                    steps.append(s); ids_per_step.append(ids); total += len(ids)
+                s += 1
+            ids_all = np.concatenate(ids_per_step)
+            keys_before, pos_before = env._mt_keys[ids_all].copy(), env._mt_pos[ids_all].copy()
+            err, raw = None, None
+            try:
+                scenes = env._sample_many(ids_all, packed=True)
+                raw = np.frombuffer(scenes, np.uint8).reshape(len(ids_all), nscene)
+            except Exception as exc:       # noqa: BLE001  (PlacementError etc.: re-raised by the consumer)
+                err = exc
+            self.next_finish[ids_all] += H[ids_all]
+            off = 0
+            for s, ids in zip(steps, ids_per_step):
+                n = len(ids)
+                item = (s, ids, None if raw is None else raw[off:off + n], err, keys_before[off:off + n], pos_before[off:off + n])
+                off += n
+                with self.lock:
+                    self.items.append(item)
+                while not self.stop:
+                    try:
+                        self.q.put(item, timeout=0.05)
+                        break
+                    except queue.Full:
+                        continue
+
+    def get(self, step, finished):
+        """Scenes ([n, sizeof(mg_scene)] uint8) of the envs finishing on `step`; None if the schedule does not match
+        (the caller then cancels the feeder and samples synchronously)."""
+        item = self.q.get()
+        with self.lock:
+            self.items = [it for it in self.items if it is not item]
+        s, ids, raw, err, kb, pb = item
+        if s != step or len(ids) != len(finished) or (ids != finished).any():
+            with self.lock:
+                self.items.insert(0, item)       # not consumed: roll it back with the rest
+            return None
+        if err is not None:
+            raise err
+        return raw
+
+    def cancel(self):
+        """Stop the thread and put every stream back to where the consumed episodes left it."""
+        self.stop = True
+        while self.thread.is_alive():
+            try:
+                self.q.get_nowait()
+            except queue.Empty:
+                pass
+            self.thread.join(timeout=0.01)
+        env = self.env
+        for s, ids, raw, err, kb, pb in reversed(self.items):
+            env._mt_keys[ids], env._mt_pos[ids] = kb, pb
+        self.items = []
 
 
 class BatchedMagicalEnv:
@@ -102,9 +212,18 @@ class BatchedMagicalEnv:
             self._done = torch.zeros(B, dtype=torch.uint8, device=self.device)
             self._actions = torch.zeros(B, dtype=torch.int32, device=self.device)
         self._extra = {}
+        self._feeder = None
+        # auto-reset samples the coming episodes on a host thread while the GPU steps (False: synchronously, on the
+        # step that needs them; same scenes either way)
+        self.async_reset = not self._py_reset
+        # optional override of where auto-reset takes its scenes from: callable(env_indices) -> [n, sizeof(mg_scene)]
+        # uint8 (bench.py's fixed-count scene pool); None: the envs' own RandomState streams
+        self.reset_source = None
+        self._abs_step = 0
+        self._spec_bytes = None
         self.seed(seed)
         self._episode_steps = np.zeros(B, np.int64)
-        self.scenes = [None] * B
+        self._scene_raw = np.zeros((B, C.sizeof(L.Scene)), np.uint8)
         self._needs_reset = True
 
     @staticmethod
@@ -122,7 +241,18 @@ class BatchedMagicalEnv:
     def _check(self, rc):
         L.check(self._h, rc)
 
+    @property
+    def scenes(self):
+        """The scene (initial state) every env was last reset to: list-like of ctypes Scene copies."""
+        return _SceneView(self._scene_raw)
+
+    def _cancel_feeder(self):
+        if self._feeder is not None:
+            self._feeder.cancel()
+            self._feeder = None
+
     def close(self):
+        self._cancel_feeder()
         if getattr(self, '_h', None) is not None and self._h:
             self._lib.mg_destroy(self._h)
             self._h = None
@@ -136,6 +266,7 @@ class BatchedMagicalEnv:
     # ------------------------------------------------------------------ reset
     def seed(self, seed=None):
         """BaseEnv.seed (base_env.py:134-141); env i gets RandomState(seed + i)."""
+        self._cancel_feeder()
         if seed is None:
             seed = np.random.randint(0, (1 << 31) - 1)
         self._seed = int(seed)
@@ -152,6 +283,7 @@ class BatchedMagicalEnv:
     @property
     def rngs(self):
         """np.random.RandomState per env, positioned where the env's stream currently is (copies)."""
+        self._cancel_feeder()      # rolls back the draws of episodes that have not started yet
         out = []
         for i in range(self.num_envs):
             r = np.random.RandomState(0)
@@ -194,13 +326,19 @@ class BatchedMagicalEnv:
             out = [self._sample(int(i)) for i in env_ids]
             return L.scenes_array(out) if packed else out
         n = len(env_ids)
-        specs = (L.ResetSpec * n)(*[self._reset_spec(int(i)) for i in env_ids])
+        if self._spec_bytes is None:
+            sb = np.zeros((self.num_envs, C.sizeof(L.ResetSpec)), np.uint8)
+            for i in range(self.num_envs):
+                sb[i] = np.frombuffer(self._reset_spec(i), np.uint8)
+            self._spec_bytes = sb
+        specs_np = np.ascontiguousarray(self._spec_bytes[env_ids])
+        specs = (L.ResetSpec * n).from_buffer(specs_np)
         keys = np.ascontiguousarray(self._mt_keys[env_ids])
         pos = np.ascontiguousarray(self._mt_pos[env_ids])
         scenes = (L.Scene * n)()
         status = np.zeros(n, np.int32)
         rc = self._lib.mg_host_sample_scenes(C.addressof(specs), n, keys.ctypes.data, pos.ctypes.data,
-                                             C.addressof(scenes), status.ctypes.data, self._reset_threads)
+                                             C.addressof(scenes), status.ctypes.data, max(1, min(self._reset_threads, n // 8)))
         if rc != 0:
             raise L.MgError(f'mg_host_sample_scenes failed ({rc})')
         for _ in range(self.placement_retries):
@@ -224,28 +362,87 @@ class BatchedMagicalEnv:
 
     def set_scenes(self, env_ids, scenes):
         """Install explicit initial states (used by reset and by the parity tests)."""
-        env_ids = np.ascontiguousarray(env_ids, np.int32)
-        arr = L.scenes_array(scenes)
-        self._check(self._lib.mg_set_scenes(self._h, env_ids.ctypes.data, len(scenes), C.addressof(arr), self._stream()))
-        for i, s in zip(env_ids.tolist(), scenes):
-            self.scenes[i] = L.copy_scene(s)
-            self._episode_steps[i] = 0
+        self.set_scenes_packed(env_ids, L.scenes_array(list(scenes)), len(scenes))
 
     def set_scenes_packed(self, env_ids, packed, n):
         """Same as set_scenes for a pre-packed ctypes array of Scene (reset pools)."""
+        self._cancel_feeder()
         env_ids = np.ascontiguousarray(env_ids, np.int32)
         self._check(self._lib.mg_set_scenes(self._h, env_ids.ctypes.data, int(n), C.addressof(packed), self._stream()))
+        self._scene_raw[env_ids] = np.frombuffer(packed, np.uint8)[:int(n) * C.sizeof(L.Scene)].reshape(int(n), -1)
         self._episode_steps[env_ids] = 0
 
     def reset(self, scenes=None):
+        self._cancel_feeder()
+        ids = np.arange(self.num_envs)
         if scenes is None:
-            scenes = self._sample_many(np.arange(self.num_envs))
-        self.set_scenes(np.arange(self.num_envs), scenes)
+            self.set_scenes_packed(ids, self._sample_many(ids, packed=True), self.num_envs)
+        else:
+            self.set_scenes(ids, scenes)
         self._check(self._lib.mg_reset_obs(self._h, L.ptr(self._obs), self._stream()))
         self._needs_reset = False
         return self._make_obs()
 
     # ------------------------------------------------------------------ step
+    def _next_scenes(self, finished):
+        """[n, sizeof(mg_scene)] uint8: the next initial states of the envs finishing on the coming step, from the
+        feeder thread (sampled while earlier steps ran) or, failing that, sampled now."""
+        if self.reset_source is not None:
+            return np.asarray(self.reset_source(finished), np.uint8).reshape(len(finished), -1)
+        if self.async_reset:
+            if self._feeder is None:
+                self._feeder = _ResetFeeder(self)
+            raw = self._feeder.get(self._abs_step + 1, finished)
+            if raw is not None:
+                return raw
+            self._cancel_feeder()          # the schedule was changed under the feeder: start over
+        packed = self._sample_many(finished, packed=True)
+        return np.frombuffer(packed, np.uint8).reshape(len(finished), -1)
+
+    def _queue_resets(self, extra=None):
+        """Auto-reset: hand the next episodes of the envs that finish on the coming step (plus `extra`, envs the caller
+        wants restarted on that step) to mg_queue_resets: they are installed between that step's physics and its
+        render.  Returns the env indices."""
+        finished = np.nonzero(self._episode_steps + 1 >= self._horizons)[0]
+        if extra is not None and len(extra):
+            finished = np.union1d(finished, np.asarray(extra, np.int64))
+        if len(finished):
+            raw = np.ascontiguousarray(self._next_scenes(finished))
+            ids32 = finished.astype(np.int32)
+            self._check(self._lib.mg_queue_resets(self._h, ids32.ctypes.data, len(finished), raw.ctypes.data, self._stream()))
+            self._scene_raw[finished] = raw
+        return finished
+
+    def step_into(self, actions, reward, done, score, restart=None):
+        """step() without the conveniences: `actions` is an int32 CUDA tensor, results go into the caller's tensors
+        (f32 / u8 / f32, CUDA) and the observation into the env's own buffer (returned by `observation()`); nothing
+        is cloned or converted.  Used by roll-out loops that own their buffers (bench.py).  `restart`: env indices to
+        restart on this step although they have not reached their horizon (auto_reset only)."""
+        if self._needs_reset:
+            raise RuntimeError('call reset() before step()')
+        st = self._stream()
+        if self._obs is not None:
+            finished = self._queue_resets(restart) if self.auto_reset else ()
+            if not self.auto_reset:
+                self._cancel_feeder()
+            self._check(self._lib.mg_step(self._h, L.ptr(actions), L.ptr(self._obs), L.ptr(reward), L.ptr(done), L.ptr(score), st))
+            self._episode_steps += 1
+            self._abs_step += 1
+            if len(finished):
+                self._episode_steps[finished] = 0
+            return
+        # no preprocessor (full-resolution observations are rendered on demand): physics, resets, ring-less render
+        self._check(self._lib.mg_step_physics(self._h, L.ptr(actions), L.ptr(reward), L.ptr(done), L.ptr(score), st))
+        self._episode_steps += 1
+        self._abs_step += 1
+        finished = np.nonzero(self._episode_steps >= self._horizons)[0]
+        if len(finished) and self.auto_reset:
+            self.set_scenes_packed(finished, self._sample_many(finished, packed=True), len(finished))
+        self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
+
+    def observation(self):
+        return self._make_obs()
+
     def step(self, actions):
         torch = _torch()
         if self._needs_reset:
@@ -256,31 +453,25 @@ class BatchedMagicalEnv:
                 raise KeyError(f'actions must be {self.num_envs} ints in [0, {L.NUM_ACTIONS})')
             self._actions.copy_(torch.from_numpy(a.astype(np.int32)), non_blocking=False)
             actions = self._actions
-        st = self._stream()
-        if self._obs is not None and not (self.auto_reset and (self._episode_steps + 1 >= self._horizons).any()):
-            # no env finishes on this step: the one-call step (render of finished parts under the physics tail)
-            self._check(self._lib.mg_step(self._h, L.ptr(actions), L.ptr(self._obs), L.ptr(self._reward), L.ptr(self._done),
-                                          L.ptr(self._score), st))
-            self._episode_steps += 1
-            # clones on every path: the internal buffers are overwritten by the next step (B floats, negligible)
-            return self._make_obs(), self._reward.clone(), self._done.bool(), {'eval_score': self._score.clone()}
-        self._check(self._lib.mg_step_physics(self._h, L.ptr(actions), L.ptr(self._reward), L.ptr(self._done),
-                                              L.ptr(self._score), st))
-        self._episode_steps += 1
-        finished = np.nonzero(self._episode_steps >= self._horizons)[0]
-        reward, done, score = self._reward.clone(), self._done.bool(), self._score.clone()
-        if len(finished) and self.auto_reset:
-            self.set_scenes(finished, self._sample_many(finished))
-        self._check(self._lib.mg_step_render(self._h, L.ptr(self._obs), st))
-        return self._make_obs(), reward, done, {'eval_score': score}
+        self.step_into(actions, self._reward, self._done, self._score)
+        # clones on every path: the internal buffers are overwritten by the next step (B floats, negligible)
+        return self._make_obs(), self._reward.clone(), self._done.bool(), {'eval_score': self._score.clone()}
 
     def step_host(self, actions_host, obs_host, reward_host, done_host, score_host):
         """mg_step_host: one env-step with HOST buffers (numpy / pinned torch CPU tensors); the H2D copy of
-        the actions and the D2H copies of obs / reward / done / eval_score are inside the call.
-        No auto-reset: the caller resets finished envs with set_scenes*."""
+        the actions and the D2H copies of obs / reward / done / eval_score are inside the call.  With auto_reset the
+        envs that finish on this step start their next episode inside it, as in step()."""
+        finished = ()
+        if self.auto_reset and self._obs is not None:
+            finished = self._queue_resets()
+        else:
+            self._cancel_feeder()
         self._check(self._lib.mg_step_host(self._h, L.ptr(actions_host), L.ptr(obs_host), L.ptr(reward_host),
                                            L.ptr(done_host), L.ptr(score_host)))
         self._episode_steps += 1
+        self._abs_step += 1
+        if len(finished):
+            self._episode_steps[finished] = 0
 
     def set_timing(self, enable):
         self._check(self._lib.mg_set_timing(self._h, int(enable)))
@@ -367,6 +558,7 @@ class BatchedMagicalEnv:
 
     def set_state(self, state, env_ids=None):
         ids = np.arange(self.num_envs, dtype=np.int32) if env_ids is None else np.ascontiguousarray(env_ids, np.int32)
+        self._cancel_feeder()
         buf = np.ascontiguousarray(state['blobs'], np.uint8)
         self._check(self._lib.mg_set_state(self._h, ids.ctypes.data, len(ids), buf.ctypes.data))
         self._episode_steps[ids] = state['episode_steps']
