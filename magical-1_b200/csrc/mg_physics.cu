@@ -15,7 +15,7 @@
  * The env's bodies, constraints and shape list are staged in shared memory for the whole step; items that
  * do not depend on each other (bodies, shape pairs, pre-steps) are spread over the group's lanes, and the
  * order-dependent half of every sub-step runs on one lane per env, the lanes of all envs of a CTA side by
- * side in warp 0 (space_step_parallel / space_step_serial).  Every scalar goes through the same operations
+ * side in warp 0 (space_step_parallel; solve_lead / solve_helper).  Every scalar goes through the same operations
  * in the same order as in a serial cpSpaceStep, so the result does not depend on the mapping.
  */
 #include <cuda_runtime.h>
@@ -475,12 +475,6 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 #ifndef PHYS_DBG_SKIP
 #define PHYS_DBG_SKIP 0    /* timing experiments only: 1 skips the serial half, 2 the parallel half, 3 the pair loop, 4 boxes + pair loop, 5 constraint pre-steps, 6 position integration */
 #endif
-#ifndef PHYS_REGSOLVER
-#define PHYS_REGSOLVER 1   /* robot constraints with body velocities in registers */
-#endif
-#ifndef PHYS_BARRIER
-#define PHYS_BARRIER 1     /* serial halves of all envs of a CTA share warp 0 */
-#endif
 #ifndef PHYS_LANES
 #define PHYS_LANES 16
 #endif
@@ -492,7 +486,7 @@ __device__ void arb_copy(EnvRef e, int dst, int src)
 
 /* cpSpaceStep(space, dt), first half, one group of PHYS_LANES lanes per env: the phases with independent items (bodies, shape
  * pairs, pre-steps) spread over the lanes.  Whatever depends on Chipmunk's order runs on one lane in that
- * order (arbiter cache updates here, the rest in space_step_serial), so the result is the same bit pattern a
+ * order (arbiter cache updates here, the rest in solve_lead / solve_helper), so the result is the same bit pattern a
  * serial cpSpaceStep produces.  `order` = shared scratch [MG_NARB + 8]; returns the number of live arbiters. */
 /* ------------------------------------------------------------------ group-cooperative narrow phase
  * The lanes of an env's group search the faces / feature pairs of ONE shape pair together.  Every candidate
@@ -924,87 +918,187 @@ __device__ __forceinline__ void reg_motor(BodyV (&r)[MG_RB_COUNT], double *cf)
     r[B].w = r[B].w + j * r[B].iinv;
 }
 
-/* one sequential-impulse pass over the robot's constraints c0 .. c0+9 (add order of setup_robot) */
-__device__ __forceinline__ void robot_constraints_pass(BodyV (&r)[MG_RB_COUNT], double *cf0)
+/* ---- the same formulas with the coefficients of a constraint loaded ahead of their use.
+ * The chain through the robot body is latency-bound, and between two constraints sit divergent branches (clamps, the
+ * limit joint's early return) that the compiler does not move loads across: each constraint then starts with a
+ * shared-memory round trip on the critical path.  robot_constraints_pass therefore loads constraint k + 1's coefficients
+ * (PivotC / ScalarC) before it applies constraint k.  Values and operation order are those of reg_pivot ... reg_motor. */
+struct PivotC { double jmax, r1x, r1y, r2x, r2y, bx, by, k0, k1, k2, k3, jx, jy, ma, ia, mb, ib; };
+struct ScalarC { double jmax, p, bias, isum, jx, ia, ib; };   /* p: gear ratio | spring w_coef | motor rate;  bias: spring target_wrn */
+/* (ma, ia, mb, ib: inverse mass / inertia of the constraint's two bodies.  They are constants of the step, so they ride
+ * with the prefetched coefficients instead of occupying registers through the whole iteration loop.) */
+struct BodyVel { double vx, vy, w; };
+
+/* bd: the env's body block in shared memory; A, B: robot-group body indices (MG_RB_*) */
+template <int A, int B>
+__device__ __forceinline__ PivotC ld_pivot(const double *cf, const double *bd)
 {
-    reg_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 0 * C_NF);
-    reg_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 1 * C_NF);
-    reg_spring<MG_RB_ROBOT, MG_RB_PUPIL_L>(r, cf0 + 2 * C_NF);
-    reg_spring<MG_RB_ROBOT, MG_RB_PUPIL_R>(r, cf0 + 3 * C_NF);
-    reg_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 4 * C_NF);
-    reg_limit<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 5 * C_NF);
-    reg_motor<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 6 * C_NF);
-    reg_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 7 * C_NF);
-    reg_limit<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 8 * C_NF);
-    reg_motor<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF);
+    const double *ba = bd + (MG_BODY_ROBOT + A) * B_NF, *bb = bd + (MG_BODY_ROBOT + B) * B_NF;
+    PivotC c = { cf[C_JMAX], cf[C_R1X], cf[C_R1Y], cf[C_R2X], cf[C_R2Y], cf[C_BIASX], cf[C_BIASY],
+                 cf[C_K0], cf[C_K1], cf[C_K2], cf[C_K3], cf[C_JX], cf[C_JY], ba[B_MINV], ba[B_IINV], bb[B_MINV], bb[B_IINV] };
+    return c;
+}
+template <int A, int B>
+__device__ __forceinline__ ScalarC ld_scalar(const double *cf, const double *bd, int kind)
+{
+    const double *ba = bd + (MG_BODY_ROBOT + A) * B_NF, *bb = bd + (MG_BODY_ROBOT + B) * B_NF;
+    ScalarC c;
+    c.jmax = cf[C_JMAX]; c.isum = cf[C_ISUM]; c.jx = cf[C_JX]; c.ia = ba[B_IINV]; c.ib = bb[B_IINV];
+    c.p = kind == CON_GEAR ? cf[C_P1] : cf[C_P0];
+    c.bias = kind == CON_SPRING ? cf[C_BIASY] : cf[C_BIASX];
+    return c;
+}
+
+template <int A, int B>
+__device__ __forceinline__ void ap_pivot(BodyVel (&r)[MG_RB_COUNT], const PivotC &c, double *cf)
+{
+    vec2 r1 = V(c.r1x, c.r1y), r2 = V(c.r2x, c.r2y);
+    vec2 v1 = vadd(V(r[A].vx, r[A].vy), vmul(vperp(r1), r[A].w));
+    vec2 v2 = vadd(V(r[B].vx, r[B].vy), vmul(vperp(r2), r[B].w));
+    vec2 vr = vsub(v2, v1);
+    vec2 d = vsub(V(c.bx, c.by), vr);
+    vec2 j = V(d.x * c.k0 + d.y * c.k1, d.x * c.k2 + d.y * c.k3);
+    vec2 j_old = V(c.jx, c.jy);
+    vec2 j_acc = vclamp_len(vadd(j_old, j), c.jmax);
+    cf[C_JX] = j_acc.x; cf[C_JY] = j_acc.y;
+    vec2 dj = vsub(j_acc, j_old), ndj = vneg(dj);
+    r[A].vx = r[A].vx + ndj.x * c.ma;
+    r[A].vy = r[A].vy + ndj.y * c.ma;
+    r[A].w = r[A].w + c.ia * vcross(r1, ndj);
+    r[B].vx = r[B].vx + dj.x * c.mb;
+    r[B].vy = r[B].vy + dj.y * c.mb;
+    r[B].w = r[B].w + c.ib * vcross(r2, dj);
+}
+template <int A, int B>
+__device__ __forceinline__ void ap_gear(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf)
+{
+    double ratio = c.p;
+    double wr = r[B].w * ratio - r[A].w;
+    double j = (c.bias - wr) * c.isum;
+    double j_old = c.jx;
+    double j_acc = dclamp(j_old + j, -c.jmax, c.jmax);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * c.ia * (1.0 / ratio);
+    r[B].w = r[B].w + j * c.ib;
+}
+template <int A, int B>
+__device__ __forceinline__ void ap_spring(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf)
+{
+    double wrn = r[A].w - r[B].w;
+    double w_damp = (c.bias - wrn) * c.p;
+    cf[C_BIASY] = wrn + w_damp;
+    double j_damp = w_damp * c.isum;
+    cf[C_JX] = c.jx + j_damp;
+    r[A].w = r[A].w + j_damp * c.ia;
+    r[B].w = r[B].w - j_damp * c.ib;
+}
+template <int A, int B>
+__device__ __forceinline__ void ap_limit(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf)
+{
+    double bias = c.bias;
+    if (!bias) return;
+    double wr = r[B].w - r[A].w;
+    double j = -(bias + wr) * c.isum;
+    double j_old = c.jx, j_acc;
+    if (bias < 0.0) j_acc = dclamp(j_old + j, 0.0, c.jmax);
+    else j_acc = dclamp(j_old + j, -c.jmax, 0.0);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * c.ia;
+    r[B].w = r[B].w + j * c.ib;
+}
+template <int A, int B>
+__device__ __forceinline__ void ap_motor(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf)
+{
+    double wr = r[B].w - r[A].w + c.p;
+    double j = -wr * c.isum;
+    double j_old = c.jx;
+    double j_acc = dclamp(j_old + j, -c.jmax, c.jmax);
+    cf[C_JX] = j_acc;
+    j = j_acc - j_old;
+    r[A].w = r[A].w - j * c.ia;
+    r[B].w = r[B].w + j * c.ib;
+}
+
+/* one sequential-impulse pass over the robot's constraints c0 .. c0+9 (add order of setup_robot) with the next
+ * constraint's coefficients loaded before the current one is applied */
+__device__ __forceinline__ void robot_constraints_pass(BodyVel (&r)[MG_RB_COUNT], double *cf0, const double *bd)
+{
+    const PivotC c0 = ld_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(cf0 + 0 * C_NF, bd);
+    const ScalarC c1 = ld_scalar<MG_RB_CONTROL, MG_RB_ROBOT>(cf0 + 1 * C_NF, bd, CON_GEAR);
+    ap_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, c0, cf0 + 0 * C_NF);
+    const ScalarC c2 = ld_scalar<MG_RB_ROBOT, MG_RB_PUPIL_L>(cf0 + 2 * C_NF, bd, CON_SPRING);
+    ap_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, c1, cf0 + 1 * C_NF);
+    const ScalarC c3 = ld_scalar<MG_RB_ROBOT, MG_RB_PUPIL_R>(cf0 + 3 * C_NF, bd, CON_SPRING);
+    ap_spring<MG_RB_ROBOT, MG_RB_PUPIL_L>(r, c2, cf0 + 2 * C_NF);
+    const PivotC c4 = ld_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(cf0 + 4 * C_NF, bd);
+    ap_spring<MG_RB_ROBOT, MG_RB_PUPIL_R>(r, c3, cf0 + 3 * C_NF);
+    const ScalarC c5 = ld_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(cf0 + 5 * C_NF, bd, CON_LIMIT);
+    ap_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, c4, cf0 + 4 * C_NF);
+    const ScalarC c6 = ld_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(cf0 + 6 * C_NF, bd, CON_MOTOR);
+    ap_limit<MG_RB_ROBOT, MG_RB_FINGER_L>(r, c5, cf0 + 5 * C_NF);
+    const PivotC c7 = ld_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(cf0 + 7 * C_NF, bd);
+    ap_motor<MG_RB_ROBOT, MG_RB_FINGER_L>(r, c6, cf0 + 6 * C_NF);
+    const ScalarC c8 = ld_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(cf0 + 8 * C_NF, bd, CON_LIMIT);
+    ap_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, c7, cf0 + 7 * C_NF);
+    const ScalarC c9 = ld_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(cf0 + 9 * C_NF, bd, CON_MOTOR);
+    ap_limit<MG_RB_ROBOT, MG_RB_FINGER_R>(r, c8, cf0 + 8 * C_NF);
+    ap_motor<MG_RB_ROBOT, MG_RB_FINGER_R>(r, c9, cf0 + 9 * C_NF);
 }
 
 /* con_apply_cached for the robot's ten constraints on the register copies (same formulas, operation for operation) */
 template <int A, int B>
-__device__ __forceinline__ void reg_cached_pivot(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)
+__device__ __forceinline__ void reg_cached_pivot(BodyVel (&r)[MG_RB_COUNT], const double *cf, const double *bd, double dt_coef)
 {
-    const vec2 j = vmul(V(cf[C_JX], cf[C_JY]), dt_coef);
-    reg_apply_impulse<A>(r, vneg(j), V(cf[C_R1X], cf[C_R1Y]));
-    reg_apply_impulse<B>(r, j, V(cf[C_R2X], cf[C_R2Y]));
+    const double *ba = bd + (MG_BODY_ROBOT + A) * B_NF, *bb = bd + (MG_BODY_ROBOT + B) * B_NF;
+    const vec2 j = vmul(V(cf[C_JX], cf[C_JY]), dt_coef), nj = vneg(j);
+    const vec2 r1 = V(cf[C_R1X], cf[C_R1Y]), r2 = V(cf[C_R2X], cf[C_R2Y]);
+    r[A].vx = r[A].vx + nj.x * ba[B_MINV];
+    r[A].vy = r[A].vy + nj.y * ba[B_MINV];
+    r[A].w = r[A].w + ba[B_IINV] * vcross(r1, nj);
+    r[B].vx = r[B].vx + j.x * bb[B_MINV];
+    r[B].vy = r[B].vy + j.y * bb[B_MINV];
+    r[B].w = r[B].w + bb[B_IINV] * vcross(r2, j);
 }
 template <int A, int B>
-__device__ __forceinline__ void reg_cached_gear(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)
+__device__ __forceinline__ void reg_cached_gear(BodyVel (&r)[MG_RB_COUNT], const double *cf, const double *bd, double dt_coef)
 {
+    const double *ba = bd + (MG_BODY_ROBOT + A) * B_NF, *bb = bd + (MG_BODY_ROBOT + B) * B_NF;
     const double j = cf[C_JX] * dt_coef;
-    r[A].w = r[A].w - j * r[A].iinv * (1.0 / cf[C_P1]);
-    r[B].w = r[B].w + j * r[B].iinv;
+    r[A].w = r[A].w - j * ba[B_IINV] * (1.0 / cf[C_P1]);
+    r[B].w = r[B].w + j * bb[B_IINV];
 }
 template <int A, int B>
-__device__ __forceinline__ void reg_cached_scalar(BodyV (&r)[MG_RB_COUNT], const double *cf, double dt_coef)   /* limit, motor */
+__device__ __forceinline__ void reg_cached_scalar(BodyVel (&r)[MG_RB_COUNT], const double *cf, const double *bd, double dt_coef)   /* limit, motor */
 {
+    const double *ba = bd + (MG_BODY_ROBOT + A) * B_NF, *bb = bd + (MG_BODY_ROBOT + B) * B_NF;
     const double j = cf[C_JX] * dt_coef;
-    r[A].w = r[A].w - j * r[A].iinv;
-    r[B].w = r[B].w + j * r[B].iinv;
+    r[A].w = r[A].w - j * ba[B_IINV];
+    r[B].w = r[B].w + j * bb[B_IINV];
 }
-__device__ __forceinline__ void robot_cached_pass(BodyV (&r)[MG_RB_COUNT], const double *cf0, double dt_coef)
+__device__ __forceinline__ void robot_cached_pass(BodyVel (&r)[MG_RB_COUNT], const double *cf0, const double *bd, double dt_coef)
 {
-    reg_cached_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 0 * C_NF, dt_coef);
-    reg_cached_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 1 * C_NF, dt_coef);
+    reg_cached_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 0 * C_NF, bd, dt_coef);
+    reg_cached_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, cf0 + 1 * C_NF, bd, dt_coef);
     /* 2, 3: damped rotary springs have no cached impulse */
-    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 4 * C_NF, dt_coef);
-    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 5 * C_NF, dt_coef);
-    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 6 * C_NF, dt_coef);
-    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 7 * C_NF, dt_coef);
-    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 8 * C_NF, dt_coef);
-    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF, dt_coef);
+    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 4 * C_NF, bd, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 5 * C_NF, bd, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_L>(r, cf0 + 6 * C_NF, bd, dt_coef);
+    reg_cached_pivot<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 7 * C_NF, bd, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 8 * C_NF, bd, dt_coef);
+    reg_cached_scalar<MG_RB_ROBOT, MG_RB_FINGER_R>(r, cf0 + 9 * C_NF, bd, dt_coef);
 }
 
-/* one sequential-impulse pass over the floor-friction pairs c_lo, c_lo + 2, .. < c_hi of the blocks (PivotJoint then
- * GearJoint between the static body and the block, Shape.setup, entities.py:700-708) with the same register
- * formulas.  The static body has zero inverse mass and inertia: every impulse leaves its velocity at +0.0, so it is
- * read once and never written. */
-__device__ __forceinline__ void block_constraints_pass(EnvRef e, int c_lo, int c_hi)
+__device__ __forceinline__ void robot_vel_load(EnvRef e, BodyVel (&r)[MG_RB_COUNT])
 {
-    BodyV r[2];
-    r[0].vx = BF(e, 0, B_VX); r[0].vy = BF(e, 0, B_VY); r[0].w = BF(e, 0, B_W);
-    r[0].minv = BF(e, 0, B_MINV); r[0].iinv = BF(e, 0, B_IINV);
-    MG_NOUNROLL
-    for (int c = c_lo; c < c_hi; c += 2) {
-        const int b = (IF(e, I_CON0 + c) >> 16) & 255;
-        r[1].vx = BF(e, b, B_VX); r[1].vy = BF(e, b, B_VY); r[1].w = BF(e, b, B_W);
-        r[1].minv = BF(e, b, B_MINV); r[1].iinv = BF(e, b, B_IINV);
-        reg_pivot<0, 1>(r, e.dc + (size_t)c * C_NF);
-        reg_gear<0, 1>(r, e.dc + (size_t)(c + 1) * C_NF);
-        BF(e, b, B_VX) = r[1].vx; BF(e, b, B_VY) = r[1].vy; BF(e, b, B_W) = r[1].w;
-    }
-}
-
-__device__ __forceinline__ void robot_regs_load(EnvRef e, BodyV (&r)[MG_RB_COUNT])
-{
-    /* fully unrolled: a rolled loop indexes r[] dynamically, which puts the whole array into local memory */
 #pragma unroll
     for (int k = 0; k < MG_RB_COUNT; k++) {
         const int b = MG_BODY_ROBOT + k;
         r[k].vx = BF(e, b, B_VX); r[k].vy = BF(e, b, B_VY); r[k].w = BF(e, b, B_W);
-        r[k].minv = BF(e, b, B_MINV); r[k].iinv = BF(e, b, B_IINV);
     }
 }
-__device__ __forceinline__ void robot_regs_store(EnvRef e, const BodyV (&r)[MG_RB_COUNT])
+__device__ __forceinline__ void robot_vel_store(EnvRef e, const BodyVel (&r)[MG_RB_COUNT])
 {
 #pragma unroll
     for (int k = 0; k < MG_RB_COUNT; k++) {
@@ -1013,81 +1107,6 @@ __device__ __forceinline__ void robot_regs_store(EnvRef e, const BodyV (&r)[MG_R
     }
 }
 
-/* the order-dependent rest of cpSpaceStep for one env, run by ONE thread: the spring pre-steps, the cached
- * impulses and the sequential-impulse iterations.  The step kernel runs this for all envs of a CTA in
- * neighbouring lanes of one warp, so that the serial chains of several envs share their instruction issue. */
-template <bool BLOCK_REG>
-__device__ void space_step_serial(EnvRef e, const unsigned char *order, int n_live, long long *tm = nullptr)
-{
-    TM_DECL(tm);
-    const int nc = IF(e, I_NCON);
-    /* cpDampedRotarySpring's pre-step applies the spring torque to both bodies: in add order.  No other
-     * pre-step reads angular velocity, so running these after the parallel ones changes nothing. */
-    MG_NOUNROLL
-    for (int c = 0; c < nc; c++)
-        if ((IF(e, I_CON0 + c) & 255) == CON_SPRING) con_prestep(e, c);
-
-    /* cpBodyUpdateVelocity: gravity 0, damping 1, no forces -> identity */
-
-    TM_ADD(TM_SPRING);
-    double dt_coef = IF(e, I_STEPPED) ? 1.0 : 0.0;  /* prev_dt == 0 ? 0 : dt / prev_dt */
-    IF(e, I_STEPPED) = 1;
-    MG_NOUNROLL
-    for (int q = 0; q < n_live; q++) arb_apply_cached(e, order, q, dt_coef);
-    MG_NOUNROLL
-    for (int c = 0; c < nc; c++) con_apply_cached(e, c, dt_coef);
-    TM_ADD(TM_CACHED);
-
-#if PHYS_REGSOLVER
-    /* constraints in add order: the robot's ten sit at c_robot, the blocks' pairs before or after them
-     * (BaseEnv.add_entities order, I_ROBOT_FIRST); block constraints only touch the static body and a block */
-    const int c_robot = IF(e, I_ROBOT_FIRST) ? 0 : nc - 10;
-    double *cf_robot = e.dc + (size_t)c_robot * C_NF;
-    BodyV r[MG_RB_COUNT];
-    robot_regs_load(e, r);
-    TM_ADD(TM_REGS);
-    MG_NOUNROLL
-    for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
-        if (n_live) {
-            /* contacts may involve any body: give them the current velocities and take theirs back */
-            robot_regs_store(e, r);
-            MG_NOUNROLL
-            for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order, q);
-            robot_regs_load(e, r);
-        }
-        TM_ADD(TM_ARB);
-        if (BLOCK_REG) block_constraints_pass(e, 0, c_robot);
-        else {
-            MG_NOUNROLL
-            for (int c = 0; c < c_robot; c++) con_apply_impulse(e, c);
-        }
-        TM_ADD(TM_BLOCKCON);
-        robot_constraints_pass(r, cf_robot);
-        TM_ADD(TM_ROBOTCON);
-        if (BLOCK_REG) block_constraints_pass(e, c_robot + 10, nc);
-        else {
-            MG_NOUNROLL
-            for (int c = c_robot + 10; c < nc; c++) con_apply_impulse(e, c);
-        }
-        TM_ADD(TM_BLOCKCON);
-    }
-    robot_regs_store(e, r);
-    TM_ADD(TM_REGS);
-    arb_pool_writeback(e, order, n_live);
-#else
-    MG_NOUNROLL
-    for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
-        MG_NOUNROLL
-        for (int q = 0; q < n_live; q++) arb_apply_impulse(e, order, q);
-        MG_NOUNROLL
-        for (int c = 0; c < nc; c++) con_apply_impulse(e, c);
-    }
-#endif
-}
-
-#ifndef PHYS_HELPERS
-#define PHYS_HELPERS 1     /* the blocks' floor-friction pairs run on the other warps, concurrently with the robot chain on warp 0 */
-#endif
 
 /* con_apply_cached for the floor-friction pair of one block (PivotJoint c, GearJoint c + 1 between the static body and
  * block body b, Shape.setup, entities.py:700-708), block side only: the static body has zero inverse mass and inertia,
@@ -1145,7 +1164,7 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
     const unsigned char *order_s = smem_env_order(k, ENVS, max_blocks, pool_n);
     int n_live = 0, c_robot = 0;
     double dt_coef = 0.0;
-    BodyV r[MG_RB_COUNT];
+    BodyVel r[MG_RB_COUNT];
     if (solver) {
         n_live = order_s[MG_NARB + 1];
         c_robot = IF(es, I_ROBOT_FIRST) ? 0 : IF(es, I_NCON) - 10;
@@ -1162,8 +1181,8 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
     if (any_live) __syncthreads();
     double *cf_robot = es.dc + (size_t)c_robot * C_NF;
     if (solver) {
-        robot_regs_load(es, r);
-        robot_cached_pass(r, cf_robot, dt_coef);
+        robot_vel_load(es, r);
+        robot_cached_pass(r, cf_robot, es.d, dt_coef);
     }
     TM_ADD(TM_CACHED);
     if (any_live) __syncthreads();
@@ -1172,19 +1191,19 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
         if (any_live) {
             if (n_live) {
                 /* contacts may involve any body: give them the current velocities and take theirs back */
-                robot_regs_store(es, r);
+                robot_vel_store(es, r);
                 MG_NOUNROLL
                 for (int q = 0; q < n_live; q++) arb_apply_impulse(es, order_s, q);
-                robot_regs_load(es, r);
+                robot_vel_load(es, r);
             }
             __syncthreads();
             TM_ADD(TM_ARB);
         }
-        if (solver) robot_constraints_pass(r, cf_robot);
+        if (solver) robot_constraints_pass(r, cf_robot, es.d);
         TM_ADD(TM_ROBOTCON);
         if (any_live) { __syncthreads(); TM_ADD(TM_BLOCKCON); }
     }
-    if (solver) { robot_regs_store(es, r); arb_pool_writeback(es, order_s, n_live); }
+    if (solver) { robot_vel_store(es, r); arb_pool_writeback(es, order_s, n_live); }
     TM_ADD(TM_REGS);
 }
 
@@ -1521,7 +1540,7 @@ __device__ __forceinline__ const unsigned char *smem_env_order(int k, int envs, 
     return ((PhysSmemFixed *)(smd + (size_t)envs * nd))[k].order;
 }
 
-template <int PHYS_THREADS_T, bool BLOCK_REG, bool PERM>
+template <int PHYS_THREADS_T, bool PERM>
 __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physics_kernel(MgDeviceState S, const int32_t *actions, float *reward,
                                                                 uint8_t *done_out, float *score_out, int max_blocks, int pool_n)
 {
@@ -1570,16 +1589,11 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     EnvRef e;
     e.d = Wd; e.dc = Wd + con_off; e.i = W->i; e.da = g.da; e.ia = g.ia;
     e.ap = Wd + pool_off; e.ainfo = W->ainfo; e.apn = pool_n;
-#if PHYS_BARRIER
-    /* lane k of warp 0 runs the serial half of the step for env k of this CTA */
+    /* lane k of warp 0 runs the robot chain and the contacts of env k of this CTA (solve_lead): it needs that env's
+     * arbiter cache in HBM */
     const bool solver = threadIdx.x < ENVS && env0 + lane < S.num_envs;
-    EnvRef es = e;
-    if (solver) {
-        const EnvRef gs = env_ref(S.dstate, S.istate, PERM ? S.perm[env0 + lane] : env0 + lane);
-        es.d = smd + (size_t)lane * nd; es.dc = es.d + con_off; es.i = sm[lane].i; es.da = gs.da; es.ia = gs.ia;
-        es.ap = es.d + pool_off; es.ainfo = sm[lane].ainfo; es.apn = pool_n;
-    }
-#if PHYS_HELPERS
+    EnvRef gs = g;
+    if (solver) gs = env_ref(S.dstate, S.istate, PERM ? S.perm[env0 + lane] : env0 + lane);
     /* the other warps: lane = (env k of the CTA, block hb of that env) runs that block's floor-friction pair */
     constexpr int SLOTS_PER_WARP = 32 / ENVS;
     static_assert((PHYS_THREADS_T / 32 - 1) * SLOTS_PER_WARP >= MG_MAX_BLOCKS, "a helper lane per block");
@@ -1587,8 +1601,6 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     EnvRef eh = e;
     eh.d = smd + (size_t)hk * nd; eh.dc = eh.d + con_off; eh.i = sm[hk].i;
     bool helper = false;          /* known once the env is staged (block count) */
-#endif
-#endif
     /* ACTION_ID_TO_FLAGS: id = ud + 3 * lr + 9 * grip (entities.py:148-190); Robot.set_action (:435-453) */
     int action = active ? actions[env] : 0;
     action = action < 0 ? 0 : (action >= MG_NUM_ACTIONS ? MG_NUM_ACTIONS - 1 : action);
@@ -1601,10 +1613,8 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     if (lr == 2) rel_turn_angle -= 1.5;
     double target_finger_angle = grip == 0 ? M_PI / 8 : -0.0;
 
-#if PHYS_BARRIER && PHYS_HELPERS
     __syncthreads();              /* every env of the CTA is staged: the helper lanes read another group's counters */
     helper = threadIdx.x >= 32 && env0 + hk < S.num_envs && hb < IF(eh, I_NBLOCKS);
-#endif
     TM_ADD(TM_STAGE);
     const int rb = MG_BODY_ROBOT;
     const int motor_l = active ? (IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6) : 0;  /* robot constraints 0..9: motors are 6 and 9 */
@@ -1634,34 +1644,16 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
             if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
             n_live_sub = n_live;
         }
-#if PHYS_BARRIER
-        /* the order-dependent halves of all envs of the CTA in neighbouring lanes of warp 0: their serial
-         * chains then cost one instruction stream instead of ENVS */
+        /* the order-dependent half of the sub-step for all envs of the CTA: robot chains and contacts side by side in
+         * warp 0, the blocks' floor-friction pairs on the other warps (solve_lead / solve_helper) */
         TM_ADD(TM_PARALLEL);
-#if PHYS_HELPERS
         const int any_live = __syncthreads_or(n_live_sub != 0);
         TM_ADD(TM_BARRIER);
-        if (threadIdx.x < 32) solve_lead<ENVS>(solver, lane & (ENVS - 1), max_blocks, pool_n, es.da, es.ia, any_live, tm_cta);
+        if (threadIdx.x < 32) solve_lead<ENVS>(solver, lane & (ENVS - 1), max_blocks, pool_n, gs.da, gs.ia, any_live, tm_cta);
         else solve_helper<ENVS>(helper, hk, hb, max_blocks, pool_n, any_live);
         TM_ADD(TM_SERIAL);
         __syncthreads();
         if (active && gl == 0) IF(e, I_STEPPED) = 1;      /* after the barrier: the helper lanes read it for dt_coef */
-#else
-        __syncthreads();
-        TM_ADD(TM_BARRIER);
-#if PHYS_DBG_SKIP != 1
-        if (solver) space_step_serial<BLOCK_REG>(es, sm[lane].order, sm[lane].order[MG_NARB + 1], tm_cta);
-#endif
-        TM_ADD(TM_SERIAL);
-        __syncthreads();
-#endif
-#else
-        if (active) {
-            /* the order-dependent half on the group's first lane; groups never wait for each other */
-            if (gl == 0) space_step_serial<BLOCK_REG>(e, W->order, W->order[MG_NARB + 1]);
-            __syncwarp(gmask);
-        }
-#endif
     }
 #ifdef MG_SECTION_TIMERS
     if (tm_cta) tm_cta[TM_TOTAL] += clock64() - tm_start;
@@ -1812,32 +1804,19 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
     const size_t smem_full = PHYS_TABLE_BYTES + per_env_bytes(MG_ARB_POOL) * PHYS_ENVS;
     if (smem_full > attr_set) {
         const int a = (int)smem_full;
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
-        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
+        cudaFuncSetAttribute(mg_physics_kernel<PHYS_THREADS / 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, a);
         attr_set = smem_full;
     }
     const int grid = (S.num_envs + envs - 1) / envs;
-    /* scenes with several blocks run the blocks' floor-friction pairs through the register formulas; with at most one
-     * block the generic constraint path measured faster (0.476 vs 0.502 ms at 4096 MoveToCorner envs).  The PERM
-     * instantiations take their envs through S.perm (mg_step in parts). */
-#define PHYS_LAUNCH(T_, R_, P_) mg_physics_kernel<T_, R_, P_><<<grid, T_, smem, st>>>(S, actions, reward, done, score, max_blocks, pool_n)
-#if PHYS_HELPERS
-    const bool block_reg = true;          /* the block pairs always run through the register formulas on their own lanes */
-#else
-    const bool block_reg = max_blocks > 1;
-#endif
+    /* the PERM instantiations take their envs through S.perm (mg_step in parts) */
+#define PHYS_LAUNCH(T_, P_) mg_physics_kernel<T_, P_><<<grid, T_, smem, st>>>(S, actions, reward, done, score, max_blocks, pool_n)
     if (S.perm) {
-        if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, true);
-        else if (block_reg) PHYS_LAUNCH(PHYS_THREADS, true, true);
-        else PHYS_LAUNCH(PHYS_THREADS, false, true);
+        if (wide) PHYS_LAUNCH(PHYS_THREADS, true); else PHYS_LAUNCH(PHYS_THREADS / 2, true);
     } else {
-        if (!wide) PHYS_LAUNCH(PHYS_THREADS / 2, true, false);
-        else if (block_reg) PHYS_LAUNCH(PHYS_THREADS, true, false);
-        else PHYS_LAUNCH(PHYS_THREADS, false, false);
+        if (wide) PHYS_LAUNCH(PHYS_THREADS, false); else PHYS_LAUNCH(PHYS_THREADS / 2, false);
     }
 #undef PHYS_LAUNCH
 }

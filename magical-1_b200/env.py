@@ -212,6 +212,7 @@ class BatchedMagicalEnv:
             self._done = torch.zeros(B, dtype=torch.uint8, device=self.device)
             self._actions = torch.zeros(B, dtype=torch.int32, device=self.device)
         self._extra = {}
+        self._res = [None, None]
         self._feeder = None
         # auto-reset samples the coming episodes on a host thread while the GPU steps (False: synchronously, on the
         # step that needs them; same scenes either way)
@@ -453,9 +454,14 @@ class BatchedMagicalEnv:
                 raise KeyError(f'actions must be {self.num_envs} ints in [0, {L.NUM_ACTIONS})')
             self._actions.copy_(torch.from_numpy(a.astype(np.int32)), non_blocking=False)
             actions = self._actions
-        self.step_into(actions, self._reward, self._done, self._score)
-        # clones on every path: the internal buffers are overwritten by the next step (B floats, negligible)
-        return self._make_obs(), self._reward.clone(), self._done.bool(), {'eval_score': self._score.clone()}
+        # results go into one of two alternating sets of buffers, so what a call returns stays valid until the call
+        # after the next one (no per-step clones; `done` is the u8 buffer viewed as bool)
+        k = self._abs_step & 1
+        if self._res[k] is None:
+            self._res[k] = (torch.zeros_like(self._reward), torch.zeros_like(self._done), torch.zeros_like(self._score))
+        reward, done, score = self._res[k]
+        self.step_into(actions, reward, done, score)
+        return self._make_obs(), reward, done.view(torch.bool), {'eval_score': score}
 
     def step_host(self, actions_host, obs_host, reward_host, done_host, score_host):
         """mg_step_host: one env-step with HOST buffers (numpy / pinned torch CPU tensors); the H2D copy of
