@@ -339,9 +339,11 @@ def run_gpu(args, rank, world, local_rank):
     n_fin = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
+    host_t0 = time.perf_counter()
     for _ in range(K):
         n_fin += int((env._episode_steps + 1 >= horizons).sum())
         dev_step()
+    host_ms = (time.perf_counter() - host_t0) * 1e3 / K      # host time to ISSUE one step (it may block on the device when it runs ahead)
     e1.record(stream)
     sync_all()
     ms_total = e0.elapsed_time(e1)
@@ -441,7 +443,7 @@ def run_gpu(args, rank, world, local_rank):
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * B * 4,
                     'd2h_bytes_per_step': world * (obs.numel() + B * 9), 'steps': Ke},
             'api': {'value': api_value, 'unit': UNIT, 'steps': Ka, 'call': 'BatchedMagicalEnv.step (auto_reset=True, device tensors)'},
-            'gpu_launches': launches,
+            'gpu_launches': launches, 'host_issue_ms_per_step': host_ms,
             'clocks': clock_info,
         }
         print(json.dumps(line), flush=True)

@@ -51,6 +51,11 @@ struct mg_handle {
     cudaEvent_t caller_ev;
     int caller_ev_used;
     int pending_queued;                      /* mg_queue_resets ran and no step has applied its resets yet */
+    /* mg_step as a CUDA graph: the fork / join of the parts is captured once per (output buffers, ring slot, scene size)
+     * and replayed, so a step costs the host one graph launch instead of ~50 kernel launches */
+    struct StepGraph { const void *obs; int slot, max_blocks, seen; cudaGraphExec_t exec; };
+    std::vector<StepGraph> graphs;
+    int step_graph;                          /* 0: launch the parts eagerly (MG_STEP_GRAPH=0) */
     /* accounting */
     int64_t launches;
     int timing;
@@ -169,6 +174,8 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
         h->step_parts = ev ? atoi(ev) : cfg->num_envs / 256;
         if (!ev && h->step_parts > 16) h->step_parts = 16;
         if (h->step_parts > MG_STEP_PARTS) h->step_parts = MG_STEP_PARTS;
+        const char *eg = getenv("MG_STEP_GRAPH");
+        h->step_graph = eg ? atoi(eg) : 1;
         const char *eo = getenv("MG_STEP_ORDER");
         h->step_order = eo ? atoi(eo) : 1;
         CK(h, cudaMalloc(&h->perm_dev, (size_t)cfg->num_envs * sizeof(int)));
@@ -193,6 +200,7 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaEventDestroy(h->fork_ev); cudaEventDestroy(h->caller_ev);
     for (int k = 0; k < 2; k++) { cudaFreeHost(h->scene_stage_host[k]); cudaFreeHost(h->ids_stage_host[k]); cudaEventDestroy(h->stage_ev[k]); }
     cudaFree(h->perm_dev);
+    for (auto &g : h->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
     for (int w = 0; w < 2; w++) for (auto &p : h->pending[w]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (auto e : h->free_events) cudaEventDestroy(e);
     delete h;
@@ -359,13 +367,11 @@ extern "C" int mg_reset_obs(mg_handle *h, uint8_t *obs_dev, void *stream) { retu
  * (an env wedged into a corner) takes 1.6x the mean, so most SMs idle through its tail, and the rasteriser of the parts
  * that are done fills that slack.  All physics parts are launched first (together they are the same single wave), then
  * geometry + raster of part k follow physics k on stream k.  Same kernels, same results; single-view HWC stacks only. */
-static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev, uint8_t *done_dev,
-                         float *score_dev, cudaStream_t st)
+/* apply_pending: the geometry pre-pass looks for queued resets (always on in a captured graph: one flag load per env) */
+static int step_parts_body(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev, uint8_t *done_dev,
+                           float *score_dev, cudaStream_t st, int view, int apply_pending)
 {
-    CK(h, cudaSetDevice(h->cfg.device));
     const int B = h->cfg.num_envs, P = h->step_parts;
-    int view = -1;
-    for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); view = v; }
     /* envs without contacts take a third of the time of an env wedged into a corner, and a CTA (a part) is as slow as
      * its slowest env: order the envs by contact load so that the light parts finish, and render, early */
     const bool ordered = h->step_order != 0;
@@ -391,13 +397,75 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
         cudaStream_t sk = h->part_stream[k];
         MgDeviceState Sr = h->S;
         if (ordered) Sr.perm = h->perm_dev;
-        mg_launch_render_push(Sr, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk, h->pending_queued != 0);
+        mg_launch_render_push(Sr, view, h->slots[view], &h->spec, h->slots, obs_dev, lo[k], lo[k + 1], sk, apply_pending);
         CK(h, cudaEventRecord(h->part_done[k], sk));
         CK(h, cudaStreamWaitEvent(st, h->part_done[k], 0));
     }
     mg_launch_clear_fresh(h->S, st);
     h->launches += 3 * P + 1 + (ordered ? 1 : 0);
-    { int rc = pending_done(h, st); if (rc != MG_OK) return rc; }
+    return MG_OK;
+}
+
+static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_dev, float *reward_dev, uint8_t *done_dev,
+                         float *score_dev, cudaStream_t st)
+{
+    CK(h, cudaSetDevice(h->cfg.device));
+    int view = -1;
+    for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); view = v; }
+    static const bool debug_sync = getenv("MG_DEBUG_SYNC") && atoi(getenv("MG_DEBUG_SYNC")) != 0;
+    int rc = MG_OK;
+    if (!h->step_graph || debug_sync) {
+        rc = step_parts_body(h, actions_dev, obs_dev, reward_dev, done_dev, score_dev, st, view, h->pending_queued != 0);
+    } else {
+        /* A graph's kernel arguments are frozen.  The observation buffer and the ring slot are part of the key (a caller
+         * that reuses one buffer needs four graphs); everything else that changes from step to step goes through the
+         * handle's own buffers: the actions are copied in before the replay and reward / done / score out after it. */
+        mg_launch_step_io(h->cfg.num_envs, actions_dev, h->actions_dev, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st);
+        h->launches++;
+        mg_handle::StepGraph *g = nullptr;
+        for (auto &c : h->graphs)
+            if (c.obs == obs_dev && c.slot == h->slots[view] && c.max_blocks == h->max_blocks) { g = &c; break; }
+        if (!g) {
+            if (h->graphs.size() >= 64) {          /* callers that never reuse their buffers: start over */
+                for (auto &c : h->graphs) if (c.exec) cudaGraphExecDestroy(c.exec);
+                h->graphs.clear();
+            }
+            h->graphs.push_back({ obs_dev, h->slots[view], h->max_blocks, 0, nullptr });
+            g = &h->graphs.back();
+        }
+        if (!g->exec && g->seen++ == 0) {
+            /* first use of this combination: eager (also sets the kernels' shared-memory attributes outside a capture) */
+            rc = step_parts_body(h, h->actions_dev, obs_dev, h->reward_dev, h->done_dev, h->score_dev, st, view, 1);
+        } else {
+            if (!g->exec) {
+                /* captured on the handle's own stream (the caller's may be the legacy default stream, which cannot
+                 * capture) and launched on the caller's */
+                cudaGraph_t graph = nullptr;
+                cudaStream_t cs = h->own_stream;
+                CK(h, cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+                const int64_t launches0 = h->launches;
+                rc = step_parts_body(h, h->actions_dev, obs_dev, h->reward_dev, h->done_dev, h->score_dev, cs, view, 1);
+                h->launches = launches0;
+                cudaError_t e = cudaStreamEndCapture(cs, &graph);
+                if (rc == MG_OK && e != cudaSuccess) rc = fail(h, MG_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+                if (rc == MG_OK) {
+                    e = cudaGraphInstantiate(&g->exec, graph, 0);
+                    if (e != cudaSuccess) rc = fail(h, MG_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+                }
+                if (graph) cudaGraphDestroy(graph);
+                if (rc != MG_OK) return rc;
+            }
+            CK(h, cudaGraphLaunch(g->exec, st));
+            h->launches += 3 * h->step_parts + 1 + (h->step_order != 0 ? 1 : 0);      /* kernel nodes of the graph */
+        }
+        if (rc == MG_OK && (reward_dev || done_dev || score_dev)) {
+            mg_launch_step_io(h->cfg.num_envs, nullptr, nullptr, h->reward_dev, reward_dev, h->done_dev, done_dev, h->score_dev, score_dev, st);
+            h->launches++;
+        }
+    }
+    if (rc != MG_OK) return rc;
+    rc = pending_done(h, st);
+    if (rc != MG_OK) return rc;
     mark_caller(h, st);
     return check_launch(h, "mg_step (parts)");
 }

@@ -47,6 +47,10 @@ struct MgObsSpec {
 
 void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const int32_t *env_ids_dev, int n, cudaStream_t st);
 void mg_launch_mark_pending(const MgDeviceState &S, const int32_t *env_ids_dev, int n, cudaStream_t st);
+/* around a graph-replayed step (whose kernel arguments are frozen): the caller's actions are copied into the handle's
+ * buffer before it, and reward / done / score from the handle's buffers to the caller's after it (NULL: not wanted) */
+void mg_launch_step_io(int n, const int32_t *actions_src, int32_t *actions_dst, const float *reward_src, float *reward_dst,
+                       const uint8_t *done_src, uint8_t *done_dst, const float *score_src, float *score_dst, cudaStream_t st);
 /* max_blocks: largest block count of any env in the batch (sizes the per-env shared-memory copy) */
 void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *reward, uint8_t *done, float *score, int max_blocks, cudaStream_t st);
 void mg_launch_score(const MgDeviceState &S, float *out, int debug_reward, cudaStream_t st);

@@ -1766,6 +1766,21 @@ void mg_launch_init(const MgDeviceState &S, const mg_scene *scenes_dev, const in
     if (n <= 0) return;
     mg_init_kernel<<<(n + 31) / 32, 32, 0, st>>>(S, scenes_dev, env_ids_dev, n);
 }
+__global__ void mg_step_io_kernel(int n, const int32_t *actions_src, int32_t *actions_dst, const float *reward_src, float *reward_dst,
+                                  const uint8_t *done_src, uint8_t *done_dst, const float *score_src, float *score_dst)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    if (actions_dst) actions_dst[k] = actions_src[k];
+    if (reward_dst) reward_dst[k] = reward_src[k];
+    if (done_dst) done_dst[k] = done_src[k];
+    if (score_dst) score_dst[k] = score_src[k];
+}
+void mg_launch_step_io(int n, const int32_t *actions_src, int32_t *actions_dst, const float *reward_src, float *reward_dst,
+                       const uint8_t *done_src, uint8_t *done_dst, const float *score_src, float *score_dst, cudaStream_t st)
+{
+    mg_step_io_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, actions_src, actions_dst, reward_src, reward_dst, done_src, done_dst, score_src, score_dst);
+}
 void mg_launch_mark_pending(const MgDeviceState &S, const int32_t *env_ids_dev, int n, cudaStream_t st)
 {
     if (n <= 0) return;
