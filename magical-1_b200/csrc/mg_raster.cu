@@ -430,6 +430,22 @@ __device__ __forceinline__ uint32_t pal_sum16(const uint32_t *pal, uint32_t w0, 
     return out;
 }
 
+/* ---- bulk asynchronous copies (sm_90+ / sm_100a copy engine): a finished 96 x 8 band (2304 contiguous bytes in shared
+ * memory, 2304 contiguous bytes in HBM) goes out as ONE cp.async.bulk instead of a per-lane loop of 16-byte stores.
+ * The issuing lane fences the warp's generic-proxy writes for the async proxy, commits the group, and waits for it
+ * before the warp exits. */
+__device__ __forceinline__ void bulk_store_fence()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store(void *dst_gmem, const void *src_smem, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 :: "l"(dst_gmem), "r"((unsigned)__cvta_generic_to_shared(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store_wait() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 struct RenderArgs {
     int view;
     int mode;            /* 0: push into the frame ring (+ optional fused stack); 1: lo-res out; 2: full-res out */
@@ -815,23 +831,26 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
 
     const size_t band_off = (size_t)band * LO_BAND_BYTES;
     if (MODE == 1) {
-        uint4 *dst = (uint4 *)(A.out + (size_t)env * MG_FRAME_BYTES + band_off);
-        RNOUNROLL
-        for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
+        if (lane == 0) {
+            bulk_store_fence();
+            bulk_store(A.out + (size_t)env * MG_FRAME_BYTES + band_off, W->lo, LO_BAND_BYTES);
+            bulk_store_commit();
+            bulk_store_wait();
+        }
         return;
     }
 
     /* mode 0: push into the frame ring.  A freshly reset env fills every slot with its first
      * frame (FlattenFrameStack.reset / EagerDictFrameStack.reset, benchmarks/__init__.py:66-74, 139-147) */
     uint8_t *ring = S.ring[A.view] + (size_t)env * MG_MAX_RING * MG_FRAME_BYTES;
-    RNOUNROLL
-    for (int s = 0; s < MG_MAX_RING; s++) {
-        if (!fresh && s != A.slot) continue;
-        uint4 *dst = (uint4 *)(ring + (size_t)s * MG_FRAME_BYTES + band_off);
+    if (lane == 0) {
+        bulk_store_fence();
         RNOUNROLL
-        for (int i = lane; i < LO_BAND_BYTES / 16; i += 32) dst[i] = ((const uint4 *)W->lo)[i];
+        for (int s = 0; s < MG_MAX_RING; s++)
+            if (fresh || s == A.slot) bulk_store(ring + (size_t)s * MG_FRAME_BYTES + band_off, W->lo, LO_BAND_BYTES);
+        bulk_store_commit();          /* in flight under the stack assembly below; waited for before the warp exits */
     }
-    if (VARIANT == 0) return;
+    if (VARIANT == 0) { if (lane == 0) bulk_store_wait(); return; }
 
     /* fused frame stack: obs[env, 8 rows of this band, 96, 3 * n_groups], channel group g taken from
      * the ring slot the host computed for (view, age).  Frames of this view that are being written
@@ -899,6 +918,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             obs_w[(size_t)q * 3 * G + w] = word;
         }
     }
+    if (lane == 0) bulk_store_wait();
 }
 
 /* generic stack composer: any mix of views, HWC or CHW (LoResStack, LoRes3EA, LoResCHW*) */

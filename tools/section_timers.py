@@ -1,6 +1,6 @@
 """Dev tool: clock64 section timers of mg_physics_kernel (build with -DMG_SECTION_TIMERS, MG_LIB_PATH selects the .so):
 per-CTA cycles of the phases of one env-step, mean and max over the CTAs, averaged over the timed steps.
-usage: MG_LIB_PATH=variants/libtimers.so MG_STEP_PARTS=1 python tools/section_timers.py [env id] [B]"""
+usage: MG_LIB_PATH=variants/libtimers.so MG_STEP_PARTS=1 python tools/section_timers.py [env id] [B] [first timed step]"""
 import ctypes as C
 import sys
 import numpy as np, torch
@@ -13,15 +13,16 @@ env = m.make(eid, num_envs=B, seed=0, obs_keys=('past_obs',))
 env.auto_reset = False
 env.reset()
 lib = env._lib
-acts = torch.randint(0, 18, (60, B), dtype=torch.int32, device='cuda', generator=torch.Generator('cuda').manual_seed(1))
+acts = torch.randint(0, 18, (80, B), dtype=torch.int32, device='cuda', generator=torch.Generator('cuda').manual_seed(1))
 NCTA = 8192
 buf = np.zeros((NCTA, 16), np.int64)
-for t in range(20):
-    env.step(acts[t])
+W0 = int(sys.argv[3]) if len(sys.argv) > 3 else 20        # steps into the episode at which the timed window starts
+for t in range(W0):
+    env.step(acts[t % 80])
 nt = lib.mg_debug_read_timers(buf.ctypes.data, NCTA)      # also clears
 steps = 40
-for t in range(20, 20 + steps):
-    env.step(acts[t])
+for t in range(W0, W0 + steps):
+    env.step(acts[t % 80])
 lib.mg_debug_read_timers(buf.ctypes.data, NCTA)
 names = ['parallel half', 'barrier wait', 'serial half', '  spring pre-steps', '  cached impulses', '  contacts (arbiters)', '  block constraints',
          '  robot constraints', 'CTA total', 'staging in', '  robot regs load/store',
