@@ -50,6 +50,19 @@
 #else
 #define RNOUNROLL
 #endif
+/* per-loop unroll factors of the few loops whose bodies are short and latency-bound (everything else stays rolled) */
+#define R_STR2(x) #x
+#define R_STR(x) R_STR2(x)
+#define R_UNROLL(n) _Pragma(R_STR(unroll n))
+#ifndef R_UNROLL_DS
+#define R_UNROLL_DS 1      /* downsample pass 1: quads per lane in flight */
+#endif
+#ifndef R_UNROLL_BG
+#define R_UNROLL_BG 1      /* background clear */
+#endif
+#ifndef R_UNROLL_SPAN
+#define R_UNROLL_SPAN 1    /* 16-byte stores of a span fill */
+#endif
 #ifndef RENDER_PREFETCH
 #define RENDER_PREFETCH 1   /* fetch the next hit's vertices while the current one is painted */
 #endif
@@ -327,7 +340,7 @@ __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t 
     RNOUNROLL
     while (x + 3 <= hi && (x & 15)) { *(uint32_t *)(row + x) = c4; x += 4; }
     const uint4 c16 = make_uint4(c4, c4, c4, c4);
-    RNOUNROLL
+    R_UNROLL(R_UNROLL_SPAN)
     for (; x + 15 <= hi; x += 16) *(uint4 *)(row + x) = c16;
     RNOUNROLL
     for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
@@ -604,7 +617,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     {
         const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
         const uint4 bg16 = make_uint4(bg4, bg4, bg4, bg4);
-        RNOUNROLL
+        R_UNROLL(R_UNROLL_BG)
         for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 16; i += 32) ((uint4 *)W->buf)[i] = bg16;
     }
     __syncwarp();
@@ -760,7 +773,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             uint32_t *lo_w = (uint32_t *)W->lo;
             uint8_t *quads = (uint8_t *)W->span_lo;                /* span_* (384 bytes) are dead by now; <= 192 entries (the mixed-block queue fills vx AND vy) */
             int n_quads = 0;
-            RNOUNROLL
+            R_UNROLL(R_UNROLL_DS)
             for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads */
                 const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
                 const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
