@@ -969,8 +969,9 @@ __device__ __forceinline__ void ap_pivot(BodyVel (&r)[MG_RB_COUNT], const PivotC
     r[B].vy = r[B].vy + dj.y * c.mb;
     r[B].w = r[B].w + c.ib * vcross(r2, dj);
 }
+/* inv_ratio = 1.0 / ratio, the division hoisted out of the iteration loop by the caller (same value every time) */
 template <int A, int B>
-__device__ __forceinline__ void ap_gear(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf)
+__device__ __forceinline__ void ap_gear(BodyVel (&r)[MG_RB_COUNT], const ScalarC &c, double *cf, double inv_ratio)
 {
     double ratio = c.p;
     double wr = r[B].w * ratio - r[A].w;
@@ -979,7 +980,7 @@ __device__ __forceinline__ void ap_gear(BodyVel (&r)[MG_RB_COUNT], const ScalarC
     double j_acc = dclamp(j_old + j, -c.jmax, c.jmax);
     cf[C_JX] = j_acc;
     j = j_acc - j_old;
-    r[A].w = r[A].w - j * c.ia * (1.0 / ratio);
+    r[A].w = r[A].w - j * c.ia * inv_ratio;
     r[B].w = r[B].w + j * c.ib;
 }
 template <int A, int B>
@@ -1023,13 +1024,13 @@ __device__ __forceinline__ void ap_motor(BodyVel (&r)[MG_RB_COUNT], const Scalar
 
 /* one sequential-impulse pass over the robot's constraints c0 .. c0+9 (add order of setup_robot) with the next
  * constraint's coefficients loaded before the current one is applied */
-__device__ __forceinline__ void robot_constraints_pass(BodyVel (&r)[MG_RB_COUNT], double *cf0, const double *bd)
+__device__ __forceinline__ void robot_constraints_pass(BodyVel (&r)[MG_RB_COUNT], double *cf0, const double *bd, double gear_inv_ratio)
 {
     const PivotC c0 = ld_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(cf0 + 0 * C_NF, bd);
     const ScalarC c1 = ld_scalar<MG_RB_CONTROL, MG_RB_ROBOT>(cf0 + 1 * C_NF, bd, CON_GEAR);
     ap_pivot<MG_RB_CONTROL, MG_RB_ROBOT>(r, c0, cf0 + 0 * C_NF);
     const ScalarC c2 = ld_scalar<MG_RB_ROBOT, MG_RB_PUPIL_L>(cf0 + 2 * C_NF, bd, CON_SPRING);
-    ap_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, c1, cf0 + 1 * C_NF);
+    ap_gear<MG_RB_CONTROL, MG_RB_ROBOT>(r, c1, cf0 + 1 * C_NF, gear_inv_ratio);
     const ScalarC c3 = ld_scalar<MG_RB_ROBOT, MG_RB_PUPIL_R>(cf0 + 3 * C_NF, bd, CON_SPRING);
     ap_spring<MG_RB_ROBOT, MG_RB_PUPIL_L>(r, c2, cf0 + 2 * C_NF);
     const PivotC c4 = ld_pivot<MG_RB_ROBOT, MG_RB_FINGER_L>(cf0 + 4 * C_NF, bd);
@@ -1186,6 +1187,7 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
     }
     TM_ADD(TM_CACHED);
     if (any_live) __syncthreads();
+    const double gear_inv_ratio = solver ? 1.0 / cf_robot[1 * C_NF + C_P1] : 1.0;     /* GearJoint control -> robot */
     MG_NOUNROLL
     for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
         if (any_live) {
@@ -1199,7 +1201,7 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
             __syncthreads();
             TM_ADD(TM_ARB);
         }
-        if (solver) robot_constraints_pass(r, cf_robot, es.d);
+        if (solver) robot_constraints_pass(r, cf_robot, es.d, gear_inv_ratio);
         TM_ADD(TM_ROBOTCON);
         if (any_live) { __syncthreads(); TM_ADD(TM_BLOCKCON); }
     }
