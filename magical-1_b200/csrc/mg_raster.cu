@@ -973,7 +973,10 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
     cudaGetDevice(&dev_);
     std::lock_guard<std::mutex> attr_lock(attr_mu);
     bool &attr_set = attr_set_dev[dev_ < 0 || dev_ >= MG_MAX_DEVICES ? 0 : dev_];
-    size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA;
+#ifndef RENDER_EXTRA_SMEM
+#define RENDER_EXTRA_SMEM 0       /* dev builds: bytes of unused shared memory per CTA, to time the kernel at lower occupancy */
+#endif
+    size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA + RENDER_EXTRA_SMEM;
     if (!attr_set) {
         cudaFuncSetAttribute(mg_render_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(mg_render_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
