@@ -63,6 +63,15 @@
 #ifndef R_UNROLL_SPAN
 #define R_UNROLL_SPAN 1    /* 16-byte stores of a span fill */
 #endif
+#ifndef RENDER_MIN_CTAS
+#define RENDER_MIN_CTAS 20   /* register cap: 5 warps per scheduler's register file (96 registers) */
+#endif
+#ifndef RENDER_REREAD
+#define RENDER_REREAD 1     /* INPLACE: the stack assembly reads the packed band back instead of keeping it in registers */
+#endif
+#ifndef RENDER_INPLACE
+#define RENDER_INPLACE 1    /* fused LoRes4 kernel: downsampled band kept inside the band buffer (see the downsample) */
+#endif
 #ifndef RENDER_PREFETCH
 #define RENDER_PREFETCH 1   /* fetch the next hit's vertices while the current one is painted */
 #endif
@@ -126,8 +135,9 @@ struct WarpSmem {
     alignas(16) uint8_t buf[BAND_ROWS * ROW_STRIDE];     /* palette indices of the band */
     int vx[MG_CIRCLE_RES + 4], vy[MG_CIRCLE_RES + 4];
     double fx[4], fy[4];                     /* float vertices (dashed outlines only) */
-    uint8_t lo[LO_BAND_BYTES];               /* downsampled band, HWC */
     int span_lo[BAND_ROWS], span_hi[BAND_ROWS], span_cnt[BAND_ROWS];   /* per-row crossings (edge-parallel fill) */
+    alignas(16) uint8_t lo[LO_BAND_BYTES];   /* downsampled band, HWC.  Last: the fused LoRes4 kernel (VARIANT 1) keeps the
+                                              * downsampled band inside `buf` and is launched without this array */
 };
 
 /* ---------------------------------------------------------------- lines (pygame draw.c) */
@@ -574,7 +584,7 @@ __global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int v
  * (the kernel is instruction-cache sensitive): 0 push into the ring; 1 push + fused 4-group HWC stack;
  * 2 push + fused generic HWC stack; 3 lo-res frame out; 4 full-res frame out */
 template <int VARIANT>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceState S, RenderArgs A)
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render_kernel(MgDeviceState S, RenderArgs A)
 {
     constexpr int MODE = VARIANT <= 2 ? 0 : VARIANT - 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -751,93 +761,97 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
         }
     }
 
-    /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block.  Blocks of one
-     * palette index (the vast majority) are a table look-up; the mixed ones are queued and summed in a
-     * second, dense pass so that one mixed block does not drag its 31 neighbours through the slow path. */
+    /* cv2.resize(INTER_AREA) at exactly 4x: round-half-even of the mean of each 4x4 block.  A lane takes four
+     * neighbouring blocks (a quad: 16 x 4 pixels -> 4 x RGB = three words).  Most quads are one colour (floor,
+     * background, the inside of a shape): those are one table look-up in pass 1; the others are queued and done 32 at
+     * a time in pass 2, whose blocks of more than one colour are in turn queued and summed densely, so that neither a
+     * quad with an edge in it nor a mixed block drags its 31 neighbours through the slow path.
+     * INPLACE (the fused LoRes4 kernel): the three words of quad (oy, ox4) overwrite the first 12 bytes of the quad's
+     * own pixels (row 4 oy, byte 16 ox4 of `buf`) as one 16-byte store, after the last read of those pixels, and the
+     * stack assembly below picks them up from there with one 16-byte load: no separate low-res array in shared
+     * memory (15 resident CTAs per SM instead of 13). */
+    constexpr bool INPLACE = VARIANT == 1 && WARPS_PER_CTA == 1 && RENDER_INPLACE;
     {
-        uint16_t *mixed = (uint16_t *)W->vx;                       /* vx, vy are dead by now: MIXED_MAX entries fill both */
-#ifdef MG_TEST_MIXED_MAX
-        const int MIXED_MAX = MG_TEST_MIXED_MAX;                   /* test builds: force the every-block fallback below */
-#else
-        const int MIXED_MAX = 4 * (MG_CIRCLE_RES + 4);
-        static_assert(sizeof(uint16_t) * 4 * (MG_CIRCLE_RES + 4) <= sizeof(W->vx) + sizeof(W->vy) && offsetof(WarpSmem, vy) == offsetof(WarpSmem, vx) + sizeof(W->vx), "mixed-block queue = vx + vy");
+        static_assert(sizeof(uint32_t) * 128 <= sizeof(W->vx) + sizeof(W->vy) && offsetof(WarpSmem, vy) == offsetof(WarpSmem, vx) + sizeof(W->vx), "mixed-block queue = vx + vy");
         static_assert(LO_ROWS * MG_LORES / 4 <= 3 * BAND_ROWS * (int)sizeof(int) && MG_CIRCLE_RES <= 3 * BAND_ROWS * (int)sizeof(int), "quad / edge lists fit span_*");
-#endif
-        int n_mixed = 0;
-        {
-            /* Pass 1, a lane takes four neighbouring blocks (a quad: 16 x 4 pixels): four 16-byte loads in, three words
-             * (4 x RGB) out; quad q = lane + 32 it, 24 quads per block row.  Most quads are one colour (floor, background,
-             * the inside of a shape): those are one table look-up; the others are queued and done block by block in a
-             * dense second pass, so that a quad with an edge in it does not drag its 31 neighbours through the slow path. */
-            const unsigned lt_mask = (1u << lane) - 1;
-            uint32_t *lo_w = (uint32_t *)W->lo;
-            uint8_t *quads = (uint8_t *)W->span_lo;                /* span_* (384 bytes) are dead by now; <= 192 entries (the mixed-block queue fills vx AND vy) */
-            int n_quads = 0;
-            R_UNROLL(R_UNROLL_DS)
-            for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads */
-                const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
-                const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
-                const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
-                const uint4 r2 = *(const uint4 *)(base + 2 * ROW_STRIDE), r3 = *(const uint4 *)(base + 3 * ROW_STRIDE);
-                const uint32_t a = r0.x;
-                const uint32_t diff = ((a ^ r0.y) | (a ^ r0.z) | (a ^ r0.w)) | ((a ^ r1.x) | (a ^ r1.y) | (a ^ r1.z) | (a ^ r1.w))
-                                      | ((a ^ r2.x) | (a ^ r2.y) | (a ^ r2.z) | (a ^ r2.w)) | ((a ^ r3.x) | (a ^ r3.y) | (a ^ r3.z) | (a ^ r3.w))
-                                      | (a ^ ((a & 255) * 0x01010101u));
-                const unsigned m = __ballot_sync(FULL, diff != 0);
-                if (diff) quads[n_quads + __popc(m & lt_mask)] = (uint8_t)q;
+        const unsigned lt_mask = (1u << lane) - 1;
+        uint32_t *lo_w = (uint32_t *)W->lo;
+        uint8_t *quads = (uint8_t *)W->span_lo;                /* span_* (384 bytes) are dead by now; <= 192 entries */
+        uint32_t *mq = (uint32_t *)W->vx;                      /* vx, vy are dead by now: the <= 128 mixed blocks of one batch of
+                                                                * quads, block id in, colour out */
+        int n_quads = 0;
+        R_UNROLL(R_UNROLL_DS)
+        for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads, 24 quads per block row */
+            const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
+            uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
+            const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
+            const uint4 r2 = *(const uint4 *)(base + 2 * ROW_STRIDE), r3 = *(const uint4 *)(base + 3 * ROW_STRIDE);
+            const uint32_t a = r0.x;
+            const uint32_t diff = ((a ^ r0.y) | (a ^ r0.z) | (a ^ r0.w)) | ((a ^ r1.x) | (a ^ r1.y) | (a ^ r1.z) | (a ^ r1.w))
+                                  | ((a ^ r2.x) | (a ^ r2.y) | (a ^ r2.z) | (a ^ r2.w)) | ((a ^ r3.x) | (a ^ r3.y) | (a ^ r3.z) | (a ^ r3.w))
+                                  | (a ^ ((a & 255) * 0x01010101u));
+            const unsigned m = __ballot_sync(FULL, diff != 0);
+            if (diff) quads[n_quads + __popc(m & lt_mask)] = (uint8_t)q;
+            else {
+                const uint32_t c = pal[a & 31];
+                if (INPLACE) *(uint4 *)base = make_uint4(c | c << 24, c >> 8 | c << 16, c >> 16 | c << 8, 0);
                 else {
-                    const uint32_t c = pal[a & 31];
                     lo_w[3 * q] = c | c << 24;
                     lo_w[3 * q + 1] = c >> 8 | c << 16;
                     lo_w[3 * q + 2] = c >> 16 | c << 8;
                 }
-                n_quads += __popc(m);
             }
-            __syncwarp();
-            /* Pass 2, the quads with more than one colour: per block, one-colour blocks by look-up, the mixed ones queued */
-            RNOUNROLL
-            for (int k0 = 0; k0 < n_quads; k0 += 32) {
-                const bool has = k0 + lane < n_quads;
-                const int q = has ? quads[k0 + lane] : 0;
-                const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
-                const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
+            n_quads += __popc(m);
+        }
+        __syncwarp();
+        /* Pass 2, the quads with more than one colour, 32 at a time: one-colour blocks by look-up, the mixed ones of the
+         * batch go through the queue (lane = block) and come back as colours */
+        RNOUNROLL
+        for (int k0 = 0; k0 < n_quads; k0 += 32) {
+            const bool has = k0 + lane < n_quads;
+            const int q = has ? quads[k0 + lane] : 0;
+            const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
+            uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
+            uint32_t w0[4];
+            int slot[4];                                        /* queue entry of block b, -1: one colour */
+            int n_mixed = 0;
+            {
                 const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
                 const uint4 r2 = *(const uint4 *)(base + 2 * ROW_STRIDE), r3 = *(const uint4 *)(base + 3 * ROW_STRIDE);
-                const uint32_t w0[4] = { r0.x, r0.y, r0.z, r0.w }, w1[4] = { r1.x, r1.y, r1.z, r1.w };
-                const uint32_t w2[4] = { r2.x, r2.y, r2.z, r2.w }, w3[4] = { r3.x, r3.y, r3.z, r3.w };
-                uint32_t rgb[4];
+                const uint32_t w1[4] = { r1.x, r1.y, r1.z, r1.w }, w2[4] = { r2.x, r2.y, r2.z, r2.w }, w3[4] = { r3.x, r3.y, r3.z, r3.w };
+                w0[0] = r0.x; w0[1] = r0.y; w0[2] = r0.z; w0[3] = r0.w;
 #pragma unroll
                 for (int b = 0; b < 4; b++) {
                     const bool mix = has && !(w0[b] == w1[b] && w0[b] == w2[b] && w0[b] == w3[b] && w0[b] == (w0[b] & 255) * 0x01010101u);
-                    rgb[b] = pal[w0[b] & 31];                /* right for a one-colour block; mixed ones are redone below */
                     const unsigned m = __ballot_sync(FULL, mix);
-                    if (mix) {
-                        const int idx = n_mixed + __popc(m & lt_mask);
-                        if (idx < MIXED_MAX) mixed[idx] = (uint16_t)(oy * MG_LORES + 4 * ox4 + b);
-                    }
+                    slot[b] = mix ? n_mixed + __popc(m & lt_mask) : -1;
+                    if (mix) mq[slot[b]] = (uint32_t)(oy * MG_LORES + 4 * ox4 + b);
                     n_mixed += __popc(m);
                 }
-                if (has) {
+            }
+            __syncwarp();
+            RNOUNROLL
+            for (int k = lane; k < n_mixed; k += 32) {
+                const int o = (int)mq[k];
+                const int my = o / MG_LORES, mx = o - my * MG_LORES;
+                const uint8_t *mb = W->buf + (4 * my) * ROW_STRIDE + 4 * mx;
+                const uint32_t v0 = *(const uint32_t *)mb, v1 = *(const uint32_t *)(mb + ROW_STRIDE);
+                const uint32_t v2 = *(const uint32_t *)(mb + 2 * ROW_STRIDE), v3 = *(const uint32_t *)(mb + 3 * ROW_STRIDE);
+                mq[k] = pal_sum16(pal, v0, v1, v2, v3);
+            }
+            __syncwarp();
+            uint32_t rgb[4];
+#pragma unroll
+            for (int b = 0; b < 4; b++) rgb[b] = slot[b] >= 0 ? mq[slot[b]] : pal[w0[b] & 31];
+            if (has) {
+                if (INPLACE) *(uint4 *)base = make_uint4(rgb[0] | rgb[1] << 24, rgb[1] >> 8 | rgb[2] << 16, rgb[2] >> 16 | rgb[3] << 8, 0);
+                else {
                     lo_w[3 * q] = rgb[0] | rgb[1] << 24;
                     lo_w[3 * q + 1] = rgb[1] >> 8 | rgb[2] << 16;
                     lo_w[3 * q + 2] = rgb[2] >> 16 | rgb[3] << 8;
                 }
             }
-        }
-        __syncwarp();
-        /* more mixed blocks than the queue holds (never seen with the reference's scenes): sum every block */
-        const bool all_blocks = n_mixed > MIXED_MAX;
-        if (all_blocks) n_mixed = LO_ROWS * MG_LORES;
-        RNOUNROLL
-        for (int k = lane; k < n_mixed; k += 32) {
-            int o = all_blocks ? k : mixed[k];
-            int oy = o / MG_LORES, ox = o % MG_LORES;
-            const uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 4 * ox;
-            uint32_t w0 = *(const uint32_t *)base, w1 = *(const uint32_t *)(base + ROW_STRIDE);
-            uint32_t w2 = *(const uint32_t *)(base + 2 * ROW_STRIDE), w3 = *(const uint32_t *)(base + 3 * ROW_STRIDE);
-            uint32_t rgb = pal_sum16(pal, w0, w1, w2, w3);
-            uint8_t *d = W->lo + o * 3;
-            d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+            __syncwarp();                                       /* the queue is reused by the next batch */
         }
     }
     __syncwarp();
@@ -856,11 +870,32 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     /* mode 0: push into the frame ring.  A freshly reset env fills every slot with its first
      * frame (FlattenFrameStack.reset / EagerDictFrameStack.reset, benchmarks/__init__.py:66-74, 139-147) */
     uint8_t *ring = S.ring[A.view] + (size_t)env * MG_MAX_RING * MG_FRAME_BYTES;
+    /* INPLACE: every lane takes its six quads of the new frame into registers (the stack assembly needs them there
+     * anyway), then the warp packs them to the front of the now dead band buffer, from where they leave like W->lo */
+    uint32_t mine[INPLACE ? PRE_IT : 1][3];
+    const uint8_t *lo_src = W->lo;
+    if (INPLACE) {
+#pragma unroll
+        for (int it = 0; it < PRE_IT; it++) {
+            const int q = lane + 32 * it;
+            const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
+            const uint4 m = *(const uint4 *)(W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4);
+            mine[it][0] = m.x; mine[it][1] = m.y; mine[it][2] = m.z;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < PRE_IT; it++) {
+            uint32_t *p = (uint32_t *)W->buf + (lane + 32 * it) * 3;
+            p[0] = mine[it][0]; p[1] = mine[it][1]; p[2] = mine[it][2];
+        }
+        __syncwarp();
+        lo_src = W->buf;
+    }
     if (lane == 0) {
         bulk_store_fence();
         RNOUNROLL
         for (int s = 0; s < MG_MAX_RING; s++)
-            if (fresh || s == A.slot) bulk_store(ring + (size_t)s * MG_FRAME_BYTES + band_off, W->lo, LO_BAND_BYTES);
+            if (fresh || s == A.slot) bulk_store(ring + (size_t)s * MG_FRAME_BYTES + band_off, lo_src, LO_BAND_BYTES);
         bulk_store_commit();          /* in flight under the stack assembly below; waited for before the warp exits */
     }
     if (VARIANT == 0) { if (lane == 0) bulk_store_wait(); return; }
@@ -872,11 +907,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
     uint32_t *obs_w = (uint32_t *)(A.obs + ((size_t)env * MG_LORES * MG_LORES + (size_t)band * LO_ROWS * MG_LORES) * C);
     if (VARIANT == 1) {
         /* LoRes4E / LoRes4A: 4 frames x RGB = 12 bytes per pixel; a lane turns 4 pixels of each frame
-         * (3 words each) into 48 contiguous output bytes = three 16-byte stores */
+         * (3 words each) into 48 contiguous output bytes = three 16-byte stores.  INPLACE: the lane's quads of the new
+         * frame are already in registers (`mine`). */
         const uint32_t *srcp[4];
+        bool cur[4];
 #pragma unroll
         for (int g = 0; g < 4; g++) {
-            if (A.gview[g] == A.view && (A.gage[g] == 0 || fresh)) srcp[g] = (const uint32_t *)W->lo;
+            cur[g] = A.gview[g] == A.view && (A.gage[g] == 0 || fresh);
+            if (cur[g]) srcp[g] = (const uint32_t *)lo_src;
             else srcp[g] = (const uint32_t *)(S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES + band_off);
         }
 #pragma unroll
@@ -886,10 +924,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) mg_render_kernel(MgDeviceS
             if (use_pre) {
 #pragma unroll
                 for (int g = 0; g < 3; g++) { src[g][0] = pre[it][g][0]; src[g][1] = pre[it][g][1]; src[g][2] = pre[it][g][2]; }
-                src[3][0] = srcp[3][q * 3]; src[3][1] = srcp[3][q * 3 + 1]; src[3][2] = srcp[3][q * 3 + 2];
+                if (INPLACE && !RENDER_REREAD) { src[3][0] = mine[it][0]; src[3][1] = mine[it][1]; src[3][2] = mine[it][2]; }
+                else { src[3][0] = srcp[3][q * 3]; src[3][1] = srcp[3][q * 3 + 1]; src[3][2] = srcp[3][q * 3 + 2]; }
             } else {
 #pragma unroll
-                for (int g = 0; g < 4; g++) { src[g][0] = srcp[g][q * 3]; src[g][1] = srcp[g][q * 3 + 1]; src[g][2] = srcp[g][q * 3 + 2]; }
+                for (int g = 0; g < 4; g++) {
+                    if (INPLACE && !RENDER_REREAD && cur[g]) { src[g][0] = mine[it][0]; src[g][1] = mine[it][1]; src[g][2] = mine[it][2]; }
+                    else { src[g][0] = srcp[g][q * 3]; src[g][1] = srcp[g][q * 3 + 1]; src[g][2] = srcp[g][q * 3 + 2]; }
+                }
             }
             uint4 *dst = (uint4 *)(obs_w + (size_t)q * 12);
 #pragma unroll
@@ -988,9 +1030,11 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
     long long items = (long long)(A.env_end - A.env_begin) * N_BANDS;
     int grid = (int)((items + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
     int variant = A.mode == 0 ? (!A.obs ? 0 : (A.n_groups == 4 ? 1 : 2)) : A.mode + 2;
+    /* the fused LoRes4 kernel keeps the downsampled band inside the band buffer: launched without WarpSmem::lo */
+    const size_t smem1 = WARPS_PER_CTA == 1 && RENDER_INPLACE ? offsetof(WarpSmem, lo) + RENDER_EXTRA_SMEM : smem;
     switch (variant) {
     case 0: mg_render_kernel<0><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
-    case 1: mg_render_kernel<1><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    case 1: mg_render_kernel<1><<<grid, WARPS_PER_CTA * 32, smem1, st>>>(S, A); break;
     case 2: mg_render_kernel<2><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
     case 3: mg_render_kernel<3><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
     default: mg_render_kernel<4><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
