@@ -266,12 +266,19 @@ __device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool
             put_px(buf, y0, x, y, c);
         }
     }
-    if (cnt <= LONG_LINE) {
+    if (cnt <= LONG_LINE && cnt > 0) {
+        /* the lane walks its own short line: floor(k * minor / major) carried from pixel to pixel (minor <= major, so
+         * at most one carry per step) instead of one division per pixel; same pixels as line_pixel */
+        const int minor = L.xmajor ? L.dyp : L.dxp;
+        const int q0 = div_small(k0 * minor, L.len, L.rmaj);
+        int rem = k0 * minor - q0 * L.len;
+        int x = L.x1 + L.sx * (L.xmajor ? k0 : q0), y = L.y1 + L.sy * (L.xmajor ? q0 : k0);
+        const int xk = L.xmajor ? L.sx : 0, yk = L.xmajor ? 0 : L.sy, xq = L.xmajor ? 0 : L.sx, yq = L.xmajor ? L.sy : 0;
         RNOUNROLL
         for (int k = k0; k <= k1; k++) {
-            int x, y;
-            line_pixel(L, k, x, y);
             put_px(buf, y0, x, y, c);
+            x += xk; y += yk; rem += minor;
+            if (rem >= L.len) { rem -= L.len; x += xq; y += yq; }
         }
     }
 }
