@@ -34,13 +34,15 @@
 #define N_BANDS (RES / BAND_ROWS)
 #define ROW_STRIDE 400                       /* 25 x 16 B: rows are 16-byte aligned and the 16-byte stores of a quarter
                                               * warp (8 lanes = 8 rows, 100 words apart) fall on distinct banks */
-#define ROW_PARTS (32 / BAND_ROWS)            /* lanes that share one row in the polygon fills */
+#ifndef WARPS_PER_BAND
+#define WARPS_PER_BAND 2      /* warps (of one CTA) that paint one band together: the kernel is bound by the latency of a
+                               * band's instruction stream at the 15 bands per SM that shared memory allows, so a second
+                               * warp on the same band buffer doubles the resident warps and shortens every band */
+#endif
+#define NT (32 * WARPS_PER_BAND)              /* threads per band = per CTA */
+#define LPR (NT / BAND_ROWS)                  /* neighbouring lanes that share one row in the polygon fills */
 #define LO_ROWS (BAND_ROWS / 4)
 #define LO_BAND_BYTES (LO_ROWS * MG_LORES * 3)   /* 2304 */
-#ifndef WARPS_PER_CTA
-#define WARPS_PER_CTA 1      /* bands differ a lot in cost: a CTA of several warps holds its shared memory until the slowest
-                              * one is done (measured at 4096 envs: 0.63 ms with 4 warps per CTA, 0.54 ms with 1) */
-#endif
 #define FULL 0xffffffffu
 #ifndef RENDER_ROLLED
 #define RENDER_ROLLED 1
@@ -64,7 +66,7 @@
 #define R_UNROLL_SPAN 1    /* 16-byte stores of a span fill */
 #endif
 #ifndef RENDER_MIN_CTAS
-#define RENDER_MIN_CTAS 20   /* register cap: 5 warps per scheduler's register file (96 registers) */
+#define RENDER_MIN_CTAS (WARPS_PER_BAND == 1 ? 20 : 15)   /* register cap: 96 registers for one warp per band, 64 for two */
 #endif
 #ifndef RENDER_REREAD
 #define RENDER_REREAD 1     /* INPLACE: the stack assembly reads the packed band back instead of keeping it in registers */
@@ -134,11 +136,18 @@ __device__ aff ego_camera(double cx, double cy, double cs, double sn)
 struct WarpSmem {
     alignas(16) uint8_t buf[BAND_ROWS * ROW_STRIDE];     /* palette indices of the band */
     int vx[MG_CIRCLE_RES + 4], vy[MG_CIRCLE_RES + 4];
+    uint32_t mq_more[128 * WARPS_PER_BAND > 2 * (MG_CIRCLE_RES + 4) ? 128 * WARPS_PER_BAND - 2 * (MG_CIRCLE_RES + 4) : 1];   /* vx + vy + this = the downsample's mixed-block queues */
     double fx[4], fy[4];                     /* float vertices (dashed outlines only) */
     int span_lo[BAND_ROWS], span_hi[BAND_ROWS], span_cnt[BAND_ROWS];   /* per-row crossings (edge-parallel fill) */
     alignas(16) uint8_t lo[LO_BAND_BYTES];   /* downsampled band, HWC.  Last: the fused LoRes4 kernel (VARIANT 1) keeps the
                                               * downsampled band inside `buf` and is launched without this array */
 };
+
+/* the threads of a band meet: a warp-level fence for one warp per band, the CTA barrier otherwise */
+__device__ __forceinline__ void band_sync()
+{
+    if (WARPS_PER_BAND == 1) __syncwarp(); else __syncthreads();
+}
 
 /* ---------------------------------------------------------------- lines (pygame draw.c) */
 
@@ -178,7 +187,15 @@ __device__ bool clipline(int &x1, int &y1, int &x2, int &y2)
  * axis by floor(k * minor_len / major_len). */
 struct Line { int x1, y1, sx, sy, dxp, dyp, len; bool xmajor; float rmaj; };
 
-/* floor(a / b) for 0 <= a < 2^24, 0 < b: one float multiply and a +-1 correction instead of an integer divide */
+/* 1 / x to within 1 ulp in one MUFU instruction; every use below corrects its quotient (div_small) or keeps a margin */
+__device__ __forceinline__ float rcp_fast(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+/* floor(a / b) for 0 <= a < 2^24, 0 < b, a / b < 2^20: one float multiply and a +-1 correction instead of an integer
+ * divide (rb = 1 / b to within a few ulp: the estimate is off by less than one) */
 __device__ __forceinline__ int div_small(int a, int b, float rb)
 {
     int q = (int)((float)a * rb);
@@ -189,7 +206,7 @@ __device__ __forceinline__ int div_small(int a, int b, float rb)
 /* C integer division (truncation toward zero) of num by den > 0 */
 __device__ __forceinline__ int div_trunc(int num, int den)
 {
-    float rb = __frcp_rn((float)den);
+    float rb = rcp_fast((float)den);
     return num >= 0 ? div_small(num, den, rb) : -div_small(-num, den, rb);
 }
 
@@ -203,7 +220,7 @@ __device__ __forceinline__ bool line_setup(int x1, int y1, int x2, int y2, Line 
     L.x1 = x1; L.y1 = y1;
     L.xmajor = !(L.dxp < L.dyp);
     L.len = L.xmajor ? L.dxp : L.dyp;
-    L.rmaj = __frcp_rn((float)L.len);
+    L.rmaj = rcp_fast((float)L.len);
     return true;
 }
 __device__ __forceinline__ void line_pixel(const Line &L, int k, int &x, int &y)
@@ -220,35 +237,40 @@ __device__ __forceinline__ void put_px(uint8_t *buf, int y0, int x, int y, uint8
 /* offsets of clip_and_draw_line_width: width 2 -> 0,+1; width 4 -> 0,+1,-1,+2 */
 __device__ __forceinline__ int width_offset(int copy) { return copy == 0 ? 0 : (copy == 1 ? 1 : (copy == 2 ? -1 : 2)); }
 
-/* One batch of up to 32 line copies, lane = job (has == false: no job).  Every lane clips and sets up its own line;
+/* One batch of up to 32 line jobs, lane = job (has == false: no job).  Every lane clips and sets up its own line;
  * lines longer than LONG_LINE pixels are then handed to the whole warp one after the other (pixels spread over the
  * lanes), the short ones are drawn by their own lanes side by side.  All copies of one outline carry the same
  * colour, so the order in which their pixels land does not matter.  The only copy of the line code in the kernel
- * (the kernel is bound by instruction fetch). */
+ * (the kernel is bound by instruction fetch).
+ * dup: the job also draws the line's second copy of a width-2 outline, the same pixels one to the right (dup == 1) or
+ * one down (dup == 2).  Only for lines that clipline leaves alone in both positions (the caller checks the end points),
+ * where the two copies are the same DDA run: one set-up for both. */
 #ifndef LONG_LINE
 #define LONG_LINE 12
 #endif
-__device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool has, int x1, int y1, int x2, int y2, uint8_t c)
+__device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool has, int x1, int y1, int x2, int y2, uint8_t c, int dup)
 {
     Line L = { 0, 0, 1, 1, 1, 1, 0, true, 1.0f };      /* len 0: nothing to draw */
-    if (has && !(max(y1, y2) < y0 || min(y1, y2) >= y0 + BAND_ROWS)) line_setup(x1, y1, x2, y2, L);   /* sets len only if the clip keeps the line */
+    const int ey = dup == 2 ? 1 : 0;                   /* the copy below reaches one row further */
+    if (has && !(max(y1, y2) + ey < y0 || min(y1, y2) >= y0 + BAND_ROWS)) line_setup(x1, y1, x2, y2, L);   /* sets len only if the clip keeps the line */
     /* pixels k0 .. k1 of the line can fall into this band: a superset (put_px still tests the row), so the picture
      * is the same, but a long steep line costs a band only its own rows instead of its whole length */
     int k0 = 0, k1 = L.len - 1;
     if (L.len > 0) {
-        /* minor-axis (x-major) or pixel (y-major) index range whose row lies in [y0, y0 + BAND_ROWS) */
-        int ta = (y0 - L.y1) * L.sy, tb = (y0 + BAND_ROWS - 1 - L.y1) * L.sy;
+        /* minor-axis (x-major) or pixel (y-major) index range whose row lies in [y0 - ey, y0 + BAND_ROWS) */
+        int ta = (y0 - ey - L.y1) * L.sy, tb = (y0 + BAND_ROWS - 1 - L.y1) * L.sy;
         if (ta > tb) { int t = ta; ta = tb; tb = t; }
         if (!L.xmajor) { k0 = max(k0, ta); k1 = min(k1, tb); }
         else if (L.dyp > 1) {
-            const float r = (float)L.dxp * __frcp_rn((float)L.dyp);
+            const float r = (float)L.dxp * rcp_fast((float)L.dyp);
             k0 = max(k0, (int)((float)max(ta, 0) * r) - 2);
             k1 = min(k1, (int)((float)(min(tb, L.dyp) + 1) * r) + 2);
         }
     }
+    const int ox = dup == 1 ? 1 : 0;
     const int cnt = k1 - k0 + 1;
     unsigned longs = __ballot_sync(FULL, cnt > LONG_LINE);
-    const int packed = (L.sx & 3) | (L.sy & 3) << 2 | (int)L.xmajor << 4;
+    const int packed = (L.sx & 3) | (L.sy & 3) << 2 | (int)L.xmajor << 4 | dup << 5;
     while (longs) {
         const int src = __ffs(longs) - 1;
         longs &= longs - 1;
@@ -259,24 +281,27 @@ __device__ __noinline__ void draw_line_jobs(uint8_t *buf, int y0, int lane, bool
         const int m0 = __shfl_sync(FULL, k0, src), m1 = __shfl_sync(FULL, k1, src);
         const int pk = __shfl_sync(FULL, packed, src);
         M.sx = (pk & 3) == 1 ? 1 : -1; M.sy = ((pk >> 2) & 3) == 1 ? 1 : -1; M.xmajor = (pk >> 4) & 1;
+        const int mdup = pk >> 5;
         RNOUNROLL
         for (int k = m0 + lane; k <= m1; k += 32) {
             int x, y;
             line_pixel(M, k, x, y);
             put_px(buf, y0, x, y, c);
+            if (mdup) put_px(buf, y0, x + (mdup == 1), y + (mdup == 2), c);
         }
     }
     if (cnt <= LONG_LINE && cnt > 0) {
         /* the lane walks its own short line: floor(k * minor / major) carried from pixel to pixel (minor <= major, so
          * at most one carry per step) instead of one division per pixel; same pixels as line_pixel */
         const int minor = L.xmajor ? L.dyp : L.dxp;
-        const int q0 = div_small(k0 * minor, L.len, L.rmaj);
+        const int q0 = k0 == 0 ? 0 : div_small(k0 * minor, L.len, L.rmaj);
         int rem = k0 * minor - q0 * L.len;
         int x = L.x1 + L.sx * (L.xmajor ? k0 : q0), y = L.y1 + L.sy * (L.xmajor ? q0 : k0);
         const int xk = L.xmajor ? L.sx : 0, yk = L.xmajor ? 0 : L.sy, xq = L.xmajor ? 0 : L.sx, yq = L.xmajor ? L.sy : 0;
         RNOUNROLL
         for (int k = k0; k <= k1; k++) {
             put_px(buf, y0, x, y, c);
+            if (dup) put_px(buf, y0, x + ox, y + ey, c);
             x += xk; y += yk; rem += minor;
             if (rem >= L.len) { rem -= L.len; x += xq; y += yq; }
         }
@@ -300,7 +325,7 @@ __device__ __forceinline__ double arange_at(double start, double step, int i)
 /* ---------------------------------------------------------------- one primitive (render.Poly) */
 
 /* Poly.draw_outline(dashed=True) for one edge (render.py:232-255): dash d joins arange point 2d+1 to 2d */
-__device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, double y1, double x2, double y2, uint8_t c)
+__device__ void draw_dashed_edge(uint8_t *buf, int y0, int tid, double x1, double y1, double x2, double y2, uint8_t c)
 {
     const double dl = 10;
     int n;
@@ -321,10 +346,11 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
         n = nx < ny ? nx : ny;
     }
     int n_dash = n / 2;
-    /* lane = (dash, copy) */
+    /* thread = (dash, copy) */
+    const int lane = tid & 31;
     RNOUNROLL
-    for (int job0 = 0; job0 < n_dash * 4; job0 += 32) {
-        const int job = job0 + lane;
+    for (int job0 = 0; job0 < n_dash * 4; job0 += NT) {
+        const int job = job0 + tid;
         const bool has = job < n_dash * 4;
         int d = job >> 2, copy = job & 3;
         double xa = sx_ != 0 ? arange_at(x1, sx_, 2 * d + 1) : x1, ya = sy_ != 0 ? arange_at(y1, sy_, 2 * d + 1) : y1;
@@ -332,56 +358,64 @@ __device__ void draw_dashed_edge(uint8_t *buf, int y0, int lane, double x1, doub
         int px1 = (int)rint(xa), py1 = (int)rint(ya), px2 = (int)rint(xb), py2 = (int)rint(yb);
         int off = width_offset(copy);
         if (abs(px1 - px2) > abs(py1 - py2)) { py1 += off; py2 += off; } else { px1 += off; px2 += off; }
-        draw_line_jobs(buf, y0, lane, has, px1, py1, px2, py2, c);
+        draw_line_jobs(buf, y0, lane, has, px1, py1, px2, py2, c, 0);
     }
 }
 
 /* drawhorzlineclip: inclusive span [lo, hi] of one row, clipped to the surface; word stores inside.
- * The 32 / BAND_ROWS lanes that share a row (part = 0 .. ROW_PARTS-1) split the span at word boundaries. */
+ * The LPR lanes that share a row (part = 0 .. LPR-1) split the span at word boundaries. */
 __device__ __forceinline__ void fill_span(uint8_t *row, int lo, int hi, uint8_t c, int part)
 {
     if (hi < 0 || lo > RES - 1) return;
     lo = max(lo, 0); hi = min(hi, RES - 1);
-    if (ROW_PARTS > 1) {
-        int chunk = (((hi - lo + 1) + ROW_PARTS - 1) / ROW_PARTS + 3) & ~3;
+    if (LPR > 1) {
+        int chunk = (((hi - lo + 1) + LPR - 1) / LPR + 3) & ~3;
         int a = lo + part * chunk;
         if (part > 0) a &= ~3;
         int b = (lo + (part + 1) * chunk) & ~3;
-        lo = a; hi = part == ROW_PARTS - 1 ? hi : min(hi, b - 1);
+        lo = a; hi = part == LPR - 1 ? hi : min(hi, b - 1);
         if (lo > hi) return;
     }
+    /* the lane owns its row (or its part of it), so the words at the two ends are read, merged under a byte mask and
+     * written back; whole words in between, 16 bytes at a time where aligned */
     const uint32_t c4 = c * 0x01010101u;
-    int x = lo;
+    uint32_t *wrow = (uint32_t *)row;
+    const int a = lo >> 2, b = hi >> 2;
+    const uint32_t ma = 0xffffffffu << (8 * (lo & 3)), mb = 0xffffffffu >> (8 * (3 - (hi & 3)));
+    if (a == b) {
+        const uint32_t m = ma & mb;
+        wrow[a] = (wrow[a] & ~m) | (c4 & m);
+        return;
+    }
+    wrow[a] = (wrow[a] & ~ma) | (c4 & ma);
+    wrow[b] = (wrow[b] & ~mb) | (c4 & mb);
+    int w = a + 1;
     RNOUNROLL
-    while (x <= hi && (x & 3)) row[x++] = c;
-    RNOUNROLL
-    while (x + 3 <= hi && (x & 15)) { *(uint32_t *)(row + x) = c4; x += 4; }
+    while (w < b && (w & 3)) wrow[w++] = c4;
     const uint4 c16 = make_uint4(c4, c4, c4, c4);
     R_UNROLL(R_UNROLL_SPAN)
-    for (; x + 15 <= hi; x += 16) *(uint4 *)(row + x) = c16;
+    for (; w + 3 < b; w += 4) *(uint4 *)(wrow + w) = c16;
     RNOUNROLL
-    for (; x + 3 <= hi; x += 4) *(uint32_t *)(row + x) = c4;
-    RNOUNROLL
-    for (; x <= hi; x++) row[x] = c;
+    for (; w < b; w++) wrow[w] = c4;
 }
 
-/* same fill for polygons with many edges (the 100-gon circles): lanes take edges, every edge adds its
+/* same fill for polygons with many edges (the 100-gon circles): threads take edges, every edge adds its
  * crossings to the rows of the band it spans; then the row's lanes fill it.  Same spans as the row-parallel form. */
-__device__ __forceinline__ void fill_poly_band_edges(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, int &lo, int &hi, int &cnt)
+__device__ __forceinline__ void fill_poly_band_edges(WarpSmem *W, int y0, int tid, int row, int n, int miny, int maxy, int &lo, int &hi, int &cnt)
 {
-    const int row = lane % BAND_ROWS;
-    if (lane < BAND_ROWS) { W->span_lo[lane] = 0x7fffffff; W->span_hi[lane] = -0x7fffffff - 1; W->span_cnt[lane] = 0; }
-    __syncwarp();
+    if (tid < BAND_ROWS) { W->span_lo[tid] = 0x7fffffff; W->span_hi[tid] = -0x7fffffff - 1; W->span_cnt[tid] = 0; }
+    band_sync();
     if (miny == maxy) {
-        int xlo = 0x7fffffff, xhi = -0x7fffffff - 1;
-        RNOUNROLL
-        for (int i = lane; i < n; i += 32) { xlo = min(xlo, W->vx[i]); xhi = max(xhi, W->vx[i]); }
-        xlo = __reduce_min_sync(FULL, xlo); xhi = __reduce_max_sync(FULL, xhi);
-        unsigned r = (unsigned)(miny - y0);
-        if (r == (unsigned)lane && lane < BAND_ROWS) { W->span_lo[lane] = xlo; W->span_hi[lane] = xhi; W->span_cnt[lane] = 2; }
+        /* polygon one pixel high: span = x extent */
+        const unsigned r = (unsigned)(miny - y0);
+        if (r < BAND_ROWS) {
+            RNOUNROLL
+            for (int i = tid; i < n; i += NT) { atomicMin(&W->span_lo[r], W->vx[i]); atomicMax(&W->span_hi[r], W->vx[i]); }
+            if (tid == 0) W->span_cnt[r] = 2;
+        }
     } else {
         RNOUNROLL
-        for (int i = lane; i < n; i += 32) {
+        for (int i = tid; i < n; i += NT) {
             int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
             int x1, y1, x2, y2;
             if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
@@ -390,7 +424,7 @@ __device__ __forceinline__ void fill_poly_band_edges(WarpSmem *W, int y0, int la
             /* rows with (y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2) */
             int ylast = y2 == maxy ? y2 : y2 - 1;
             int ya_ = max(y1, y0), yb_ = min(ylast, y0 + BAND_ROWS - 1);
-            float rb = __frcp_rn((float)(y2 - y1));
+            float rb = rcp_fast((float)(y2 - y1));
             RNOUNROLL
             for (int y = ya_; y <= yb_; y++) {
                 int num = (y - y1) * (x2 - x1);
@@ -401,35 +435,43 @@ __device__ __forceinline__ void fill_poly_band_edges(WarpSmem *W, int y0, int la
             }
         }
     }
-    __syncwarp();
+    band_sync();
     lo = W->span_lo[row]; hi = W->span_hi[row]; cnt = W->span_cnt[row];
 }
 
-/* pygame.draw.polygon fill of rows [y0, y0 + BAND_ROWS): lane owns row y0 + lane % BAND_ROWS */
-__device__ void fill_poly_band(WarpSmem *W, int y0, int lane, int n, int miny, int maxy, uint8_t c)
+/* pygame.draw.polygon fill of rows [y0, y0 + BAND_ROWS): LPR neighbouring lanes own row y0 + tid / LPR; each takes every
+ * LPR-th edge, a butterfly joins their crossings, then they split the span.  n is uniform over the band's threads. */
+__device__ void fill_poly_band(WarpSmem *W, int y0, int tid, int n, int miny, int maxy, uint8_t c)
 {
-    const int row = lane % BAND_ROWS, part = lane / BAND_ROWS;
+    const int row = tid / LPR, part = tid % LPR;
     int y = y0 + row;
     int lo = 0x7fffffff, hi = -0x7fffffff - 1, cnt = 0;
-    if (n > 8) fill_poly_band_edges(W, y0, lane, n, miny, maxy, lo, hi, cnt);
-    else if (y < miny || y > maxy) cnt = 0;
-    else if (miny == maxy) {
-        /* polygon one pixel high: span = x extent */
-        RNOUNROLL
-        for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
-        cnt = 2;
-    } else {
-        RNOUNROLL
-        for (int i = 0; i < n; i++) {
-            int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
-            int x1, y1, x2, y2;
-            if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
-            else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
-            else continue;
-            if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
-                int x = div_trunc((y - y1) * (x2 - x1), y2 - y1) + x1;
-                lo = min(lo, x); hi = max(hi, x); cnt++;
+    if (n > 8) fill_poly_band_edges(W, y0, tid, row, n, miny, maxy, lo, hi, cnt);
+    else {
+        if (y < miny || y > maxy) cnt = 0;
+        else if (miny == maxy) {
+            /* polygon one pixel high: span = x extent */
+            RNOUNROLL
+            for (int i = 0; i < n; i++) { lo = min(lo, W->vx[i]); hi = max(hi, W->vx[i]); }
+            cnt = 2;
+        } else {
+            RNOUNROLL
+            for (int i = part; i < n; i += LPR) {
+                const int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
+                int x1, y1, x2, y2;
+                if (ya < yb) { x1 = xa; y1 = ya; x2 = xb; y2 = yb; }
+                else if (ya > yb) { x1 = xb; y1 = yb; x2 = xa; y2 = ya; }
+                else continue;
+                if ((y >= y1 && y < y2) || (y == maxy && y > y1 && y <= y2)) {
+                    int x = div_trunc((y - y1) * (x2 - x1), y2 - y1) + x1;
+                    lo = min(lo, x); hi = max(hi, x); cnt++;
+                }
             }
+        }
+#pragma unroll
+        for (int d = 1; d < LPR; d <<= 1) {
+            lo = min(lo, __shfl_xor_sync(FULL, lo, d)); hi = max(hi, __shfl_xor_sync(FULL, hi, d));
+            cnt += __shfl_xor_sync(FULL, cnt, d);
         }
     }
     if (cnt < 2) return;
@@ -591,7 +633,7 @@ __global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int v
  * (the kernel is instruction-cache sensitive): 0 push into the ring; 1 push + fused 4-group HWC stack;
  * 2 push + fused generic HWC stack; 3 lo-res frame out; 4 full-res frame out */
 template <int VARIANT>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render_kernel(MgDeviceState S, RenderArgs A)
+__global__ void __launch_bounds__(NT, RENDER_MIN_CTAS) mg_render_kernel(MgDeviceState S, RenderArgs A)
 {
     constexpr int MODE = VARIANT <= 2 ? 0 : VARIANT - 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -602,27 +644,29 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
         pal[threadIdx.x] = p[0] | (p[1] << 8) | (p[2] << 16);
     }
     __syncthreads();
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    long long item = (long long)blockIdx.x * WARPS_PER_CTA + warp;
-    int env = A.env_begin + (int)(item / N_BANDS), band = (int)(item % N_BANDS);
+    /* one band per CTA; its NT threads: tid spreads data-parallel work, lane / wid matter where a warp acts as one */
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int env = A.env_begin + (int)(blockIdx.x / N_BANDS);
+    const int band = (int)(blockIdx.x % N_BANDS);
     if (env >= A.env_end) return;
     if (S.perm) env = S.perm[env];
-    WarpSmem *W = (WarpSmem *)smem_raw + warp;
+    WarpSmem *W = (WarpSmem *)smem_raw;
     const int y0 = band * BAND_ROWS;
 
     /* the fused stack reads three older frames of this band from the ring at the very end: start pulling
      * their lines towards L2 now (18 lines of 128 B per frame band) */
-    if (VARIANT == 2 && lane < LO_BAND_BYTES / 128) {
+    if (VARIANT == 2 && tid < LO_BAND_BYTES / 128) {
 #pragma unroll
         for (int g = 0; g < MG_MAX_GROUPS; g++) {
             if (g >= A.n_groups || (A.gview[g] == A.view && A.gage[g] == 0)) continue;
             const uint8_t *p = S.ring[A.gview[g]] + ((size_t)env * MG_MAX_RING + A.gslot[g]) * MG_FRAME_BYTES
-                               + (size_t)band * LO_BAND_BYTES + lane * 128;
+                               + (size_t)band * LO_BAND_BYTES + tid * 128;
             asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
         }
     }
     /* primitives in draw order, 32 headers per coalesced load; each lane tests its own primitive against
-     * the band and the warp then walks the hits in order (painter's algorithm) */
+     * the band and the band's threads then walk the hits in order (painter's algorithm).  Every warp of the band holds
+     * the same headers, so the walk is uniform over the CTA without an exchange. */
     const MgScreenPrim *sprims = S.sprims[A.view] + (size_t)env * MG_MAX_PRIMS;
     const int2 *sverts = S.sverts[A.view] + (size_t)env * MG_MAX_VERTS;
     const int np = S.n_prims[env];
@@ -635,24 +679,25 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
         const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
         const uint4 bg16 = make_uint4(bg4, bg4, bg4, bg4);
         R_UNROLL(R_UNROLL_BG)
-        for (int i = lane; i < BAND_ROWS * ROW_STRIDE / 16; i += 32) ((uint4 *)W->buf)[i] = bg16;
+        for (int i = tid; i < BAND_ROWS * ROW_STRIDE / 16; i += NT) ((uint4 *)W->buf)[i] = bg16;
     }
-    __syncwarp();
+    band_sync();
 
+    constexpr int VERT_IT = (MG_CIRCLE_RES + 1 + NT - 1) / NT;      /* vertex slots per thread: n + 1 entries, n <= MG_CIRCLE_RES */
     for (int base = 0; base < np; base += 32) {
         MgScreenPrim mine = base == 0 ? first : no_prim;
         if (base > 0 && base + lane < np) mine = sprims[base + lane];
         /* outlines reach at most 2 pixels beyond the vertex rows */
         unsigned hits = __ballot_sync(FULL, (mine.off_n & 255) != 0 && mine.maxy + 2 >= y0 && mine.miny - 2 < y0 + BAND_ROWS);
         /* vertices of the next hit are fetched while the current one is painted (HBM/L2 latency off the serial path) */
-        int2 pre_v[4];
+        int2 pre_v[VERT_IT];
 #define LOAD_VERTS(SRC)                                                                        \
         {                                                                                      \
             const int on_ = __shfl_sync(FULL, mine.off_n, (SRC));                              \
             const int nn_ = on_ & 255;                                                         \
             const int2 *pv_ = sverts + (on_ >> 8);                                             \
-            _Pragma("unroll") for (int k = 0; k < 4; k++) {                                    \
-                const int i = lane + 32 * k;                                                   \
+            _Pragma("unroll") for (int k = 0; k < VERT_IT; k++) {                              \
+                const int i = tid + NT * k;                                                    \
                 if (i <= nn_) pre_v[k] = pv_[i == nn_ ? 0 : i];                                \
             }                                                                                  \
         }
@@ -671,68 +716,83 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
         LOAD_VERTS(src)
 #endif
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int i = lane + 32 * k;
+        for (int k = 0; k < VERT_IT; k++) {
+            const int i = tid + NT * k;
             if (i <= n) { W->vx[i] = pre_v[k].x; W->vy[i] = pre_v[k].y; }     /* entry n closes the loop */
         }
-        if (P.mode == 2 && lane < 8) {
-            double d = S.dashv[A.view][((size_t)env * MG_MAX_GOALS + P.aux) * 8 + lane];
-            if (lane & 1) W->fy[lane >> 1] = d; else W->fx[lane >> 1] = d;
+        if (P.mode == 2 && tid < 8) {
+            double d = S.dashv[A.view][((size_t)env * MG_MAX_GOALS + P.aux) * 8 + tid];
+            if (tid & 1) W->fy[tid >> 1] = d; else W->fx[tid >> 1] = d;
         }
-        __syncwarp();
+        band_sync();
 #if RENDER_PREFETCH
         if (hits) LOAD_VERTS(__ffs(hits) - 1)
 #endif
         {
-            fill_poly_band(W, y0, lane, n, miny, maxy, P.fill);
-            __syncwarp();
+            fill_poly_band(W, y0, tid, n, miny, maxy, P.fill);
+            band_sync();
             if (P.mode == 1) {
                 /* solid: pygame.draw.lines(width=2) per edge = base line + copy shifted by +1 on the minor axis.
                  * Edges whose rows (+1 for the shifted copy) miss the band are dropped first, so that a 100-gon that
-                 * spans three or four bands costs each of them only the batches of its own edges. */
-                uint8_t *edges = (uint8_t *)W->span_lo;            /* <= MG_CIRCLE_RES entries of the 384 bytes of span_* */
-                int n_edges = 0;
+                 * spans three or four bands costs each of them only the batches of its own edges.  An edge whose two
+                 * copies lie inside the surface (clipline changes neither) is ONE job that draws both; the others are
+                 * two jobs, listed one after the other.  Every warp of the band builds the whole list (the same bytes,
+                 * so no exchange is needed) and then takes its share of the jobs. */
+                uint8_t *jobs = (uint8_t *)W->span_lo;             /* <= 2 * MG_CIRCLE_RES entries of the 384 bytes of span_*:
+                                                                    * edge | both << 7 */
+                int n_jobs = 0;
                 {
                     const unsigned lt = (1u << lane) - 1;
                     RNOUNROLL
                     for (int i0 = 0; i0 < n; i0 += 32) {
                         const int i = i0 + lane;
-                        bool ok = false;
+                        bool ok = false, two = false;
                         if (i < n) {
-                            const int ya = W->vy[i], yb = W->vy[i + 1];
+                            const int xa = W->vx[i], ya = W->vy[i], xb = W->vx[i + 1], yb = W->vy[i + 1];
                             ok = max(ya, yb) + 1 >= y0 && min(ya, yb) < y0 + BAND_ROWS;
+                            two = ok && ((unsigned)min(xa, xb) > RES - 2 || (unsigned)max(xa, xb) > RES - 2
+                                         || (unsigned)min(ya, yb) > RES - 2 || (unsigned)max(ya, yb) > RES - 2);
                         }
-                        const unsigned m = __ballot_sync(FULL, ok);
-                        if (ok) edges[n_edges + __popc(m & lt)] = (uint8_t)i;
-                        n_edges += __popc(m);
+                        const unsigned m = __ballot_sync(FULL, ok), m2 = __ballot_sync(FULL, two);
+                        if (ok) {
+                            const int at = n_jobs + __popc(m & lt) + __popc(m2 & lt);
+                            jobs[at] = (uint8_t)(two ? i : i | 128);
+                            if (two) jobs[at + 1] = (uint8_t)i;
+                        }
+                        n_jobs += __popc(m) + __popc(m2);
                     }
                     __syncwarp();
                 }
+                /* a warp's share: whole batches of 32 when there are many jobs, else an even split (long lines are drawn
+                 * by the warp that holds them, pixels over its lanes) */
+                const int per_warp = n_jobs >= NT ? 32 : (n_jobs + WARPS_PER_BAND - 1) / WARPS_PER_BAND;
                 RNOUNROLL
-                for (int job0 = 0; job0 < 2 * n_edges; job0 += 32) {
+                for (int job0 = wid * per_warp; job0 < n_jobs; job0 += WARPS_PER_BAND * per_warp) {
                     const int job = job0 + lane;
-                    const bool has = job < 2 * n_edges;
-                    const int i = has ? edges[job >> 1] : 0, copy = job & 1;
+                    const bool has = lane < per_warp && job < n_jobs;
+                    const int e = has ? jobs[job] : 0, i = e & 127;
+                    const int copy = has && job > 0 && jobs[job - 1] == e && !(e & 128);   /* second entry of a pair */
                     int x1 = W->vx[i], y1 = W->vy[i], x2 = W->vx[i + 1], y2 = W->vy[i + 1];
-                    if (abs(x1 - x2) > abs(y1 - y2)) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
-                    draw_line_jobs(W->buf, y0, lane, has, x1, y1, x2, y2, P.outline);
+                    const bool shift_y = abs(x1 - x2) > abs(y1 - y2);
+                    if (shift_y) { y1 += copy; y2 += copy; } else { x1 += copy; x2 += copy; }
+                    draw_line_jobs(W->buf, y0, lane, has, x1, y1, x2, y2, P.outline, (e & 128) ? (shift_y ? 2 : 1) : 0);
                 }
             } else if (P.mode == 2) {
                 RNOUNROLL
                 for (int i = 0; i < n; i++) {
                     int j = (i + 1) % n;
-                    draw_dashed_edge(W->buf, y0, lane, W->fx[i], W->fy[i], W->fx[j], W->fy[j], P.outline);
+                    draw_dashed_edge(W->buf, y0, tid, W->fx[i], W->fy[i], W->fx[j], W->fy[j], P.outline);
                 }
             }
         }
-        __syncwarp();
+        band_sync();
       }
     }
 
     if (MODE == 2) {
         /* full resolution: surfarray.array3d(...).swapaxes(0, 1) -> u8 [384, 384, 3] (render.py:394-395) */
         uint32_t *dst = (uint32_t *)(A.out + ((size_t)env * RES + y0) * RES * 3);
-        for (int g = lane; g < BAND_ROWS * (RES / 4); g += 32) {
+        for (int g = tid; g < BAND_ROWS * (RES / 4); g += NT) {
             int r = g / (RES / 4), q = g % (RES / 4);
             uint32_t w = *(const uint32_t *)(W->buf + r * ROW_STRIDE + q * 4);
             uint32_t c0 = pal[w & 31], c1 = pal[(w >> 8) & 31], c2 = pal[(w >> 16) & 31], c3 = pal[(w >> 24) & 31];
@@ -745,8 +805,8 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
     }
 
     /* 4-group stack: the three older frames of this band are needed at the very end; load them into
-     * registers now so that their HBM/L2 latency hides behind the downsample (54 words per lane) */
-    constexpr int PRE_IT = LO_ROWS * MG_LORES / 4 / 32;
+     * registers now so that their HBM/L2 latency hides behind the downsample (9 words per quad, 192 / NT quads per thread) */
+    constexpr int PRE_IT = LO_ROWS * MG_LORES / 4 / NT;
     uint32_t pre[VARIANT == 1 ? PRE_IT : 1][3][3];
     bool fresh = false, use_pre = false;
     if (MODE == 0) fresh = S.istate[mg_field_index(env, I_NF, I_FRESH)] != 0;
@@ -761,7 +821,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
                                                        + (size_t)band * LO_BAND_BYTES);
 #pragma unroll
                 for (int it = 0; it < PRE_IT; it++) {
-                    const int q = lane + 32 * it;
+                    const int q = tid + NT * it;
                     pre[it][g][0] = __ldg(p + q * 3); pre[it][g][1] = __ldg(p + q * 3 + 1); pre[it][g][2] = __ldg(p + q * 3 + 2);
                 }
             }
@@ -777,18 +837,20 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
      * own pixels (row 4 oy, byte 16 ox4 of `buf`) as one 16-byte store, after the last read of those pixels, and the
      * stack assembly below picks them up from there with one 16-byte load: no separate low-res array in shared
      * memory (15 resident CTAs per SM instead of 13). */
-    constexpr bool INPLACE = VARIANT == 1 && WARPS_PER_CTA == 1 && RENDER_INPLACE;
+    constexpr bool INPLACE = VARIANT == 1 && RENDER_INPLACE;
     {
-        static_assert(sizeof(uint32_t) * 128 <= sizeof(W->vx) + sizeof(W->vy) && offsetof(WarpSmem, vy) == offsetof(WarpSmem, vx) + sizeof(W->vx), "mixed-block queue = vx + vy");
-        static_assert(LO_ROWS * MG_LORES / 4 <= 3 * BAND_ROWS * (int)sizeof(int) && MG_CIRCLE_RES <= 3 * BAND_ROWS * (int)sizeof(int), "quad / edge lists fit span_*");
+        static_assert(offsetof(WarpSmem, vy) == offsetof(WarpSmem, vx) + sizeof(W->vx) && offsetof(WarpSmem, mq_more) == offsetof(WarpSmem, vy) + sizeof(W->vy)
+                      && sizeof(uint32_t) * 128 * WARPS_PER_BAND <= sizeof(W->vx) + sizeof(W->vy) + sizeof(W->mq_more), "mixed-block queues = vx + vy + mq_more");
+        static_assert(LO_ROWS * MG_LORES / 4 <= 3 * BAND_ROWS * (int)sizeof(int) && 2 * MG_CIRCLE_RES <= 3 * BAND_ROWS * (int)sizeof(int) && MG_CIRCLE_RES < 128, "quad / outline job lists fit span_*");
         const unsigned lt_mask = (1u << lane) - 1;
         uint32_t *lo_w = (uint32_t *)W->lo;
-        uint8_t *quads = (uint8_t *)W->span_lo;                /* span_* (384 bytes) are dead by now; <= 192 entries */
-        uint32_t *mq = (uint32_t *)W->vx;                      /* vx, vy are dead by now: the <= 128 mixed blocks of one batch of
+        /* every warp of the band keeps its own quad list and its own queue: passes 1 and 2 need no CTA barrier */
+        uint8_t *quads = (uint8_t *)W->span_lo + wid * (LO_ROWS * MG_LORES / 4 / WARPS_PER_BAND);   /* span_* (384 bytes) are dead by now; <= 192 entries */
+        uint32_t *mq = (uint32_t *)W->vx + wid * 128;          /* vx, vy are dead by now: the <= 128 mixed blocks of one batch of
                                                                 * quads, block id in, colour out */
         int n_quads = 0;
         R_UNROLL(R_UNROLL_DS)
-        for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {   /* 192 = 6 full warps of quads, 24 quads per block row */
+        for (int q = tid; q < LO_ROWS * MG_LORES / 4; q += NT) {   /* 192 = 6 full warps of quads, 24 quads per block row */
             const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
             uint8_t *base = W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4;
             const uint4 r0 = *(const uint4 *)base, r1 = *(const uint4 *)(base + ROW_STRIDE);
@@ -861,11 +923,11 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
             __syncwarp();                                       /* the queue is reused by the next batch */
         }
     }
-    __syncwarp();
+    band_sync();
 
     const size_t band_off = (size_t)band * LO_BAND_BYTES;
     if (MODE == 1) {
-        if (lane == 0) {
+        if (tid == 0) {
             bulk_store_fence();
             bulk_store(A.out + (size_t)env * MG_FRAME_BYTES + band_off, W->lo, LO_BAND_BYTES);
             bulk_store_commit();
@@ -884,28 +946,28 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
     if (INPLACE) {
 #pragma unroll
         for (int it = 0; it < PRE_IT; it++) {
-            const int q = lane + 32 * it;
+            const int q = tid + NT * it;
             const int oy = q / (MG_LORES / 4), ox4 = q - oy * (MG_LORES / 4);
             const uint4 m = *(const uint4 *)(W->buf + (4 * oy) * ROW_STRIDE + 16 * ox4);
             mine[it][0] = m.x; mine[it][1] = m.y; mine[it][2] = m.z;
         }
-        __syncwarp();
+        band_sync();
 #pragma unroll
         for (int it = 0; it < PRE_IT; it++) {
-            uint32_t *p = (uint32_t *)W->buf + (lane + 32 * it) * 3;
+            uint32_t *p = (uint32_t *)W->buf + (tid + NT * it) * 3;
             p[0] = mine[it][0]; p[1] = mine[it][1]; p[2] = mine[it][2];
         }
-        __syncwarp();
+        band_sync();
         lo_src = W->buf;
     }
-    if (lane == 0) {
+    if (tid == 0) {
         bulk_store_fence();
         RNOUNROLL
         for (int s = 0; s < MG_MAX_RING; s++)
             if (fresh || s == A.slot) bulk_store(ring + (size_t)s * MG_FRAME_BYTES + band_off, lo_src, LO_BAND_BYTES);
         bulk_store_commit();          /* in flight under the stack assembly below; waited for before the warp exits */
     }
-    if (VARIANT == 0) { if (lane == 0) bulk_store_wait(); return; }
+    if (VARIANT == 0) { if (tid == 0) bulk_store_wait(); return; }
 
     /* fused frame stack: obs[env, 8 rows of this band, 96, 3 * n_groups], channel group g taken from
      * the ring slot the host computed for (view, age).  Frames of this view that are being written
@@ -926,7 +988,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
         }
 #pragma unroll
         for (int it = 0; it < PRE_IT; it++) {
-            const int q = lane + 32 * it;
+            const int q = tid + NT * it;
             uint32_t src[4][3];
             if (use_pre) {
 #pragma unroll
@@ -959,7 +1021,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
             }
         }
     } else
-    for (int q = lane; q < LO_ROWS * MG_LORES / 4; q += 32) {      /* q = group of 4 consecutive pixels */
+    for (int q = tid; q < LO_ROWS * MG_LORES / 4; q += NT) {      /* q = group of 4 consecutive pixels */
         uint32_t src[MG_MAX_GROUPS][3];
         for (int g = 0; g < G; g++) {
             const uint32_t *p;
@@ -980,7 +1042,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32, RENDER_MIN_CTAS) mg_render
             obs_w[(size_t)q * 3 * G + w] = word;
         }
     }
-    if (lane == 0) bulk_store_wait();
+    if (tid == 0) bulk_store_wait();
 }
 
 /* generic stack composer: any mix of views, HWC or CHW (LoResStack, LoRes3EA, LoResCHW*) */
@@ -1025,7 +1087,7 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
 #ifndef RENDER_EXTRA_SMEM
 #define RENDER_EXTRA_SMEM 0       /* dev builds: bytes of unused shared memory per CTA, to time the kernel at lower occupancy */
 #endif
-    size_t smem = sizeof(WarpSmem) * WARPS_PER_CTA + RENDER_EXTRA_SMEM;
+    size_t smem = sizeof(WarpSmem) + RENDER_EXTRA_SMEM;
     if (!attr_set) {
         cudaFuncSetAttribute(mg_render_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(mg_render_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1034,17 +1096,17 @@ static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStrea
         cudaFuncSetAttribute(mg_render_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = true;
     }
-    long long items = (long long)(A.env_end - A.env_begin) * N_BANDS;
-    int grid = (int)((items + WARPS_PER_CTA - 1) / WARPS_PER_CTA);
+    /* one CTA of NT threads per band */
+    const int grid = (A.env_end - A.env_begin) * N_BANDS;
     int variant = A.mode == 0 ? (!A.obs ? 0 : (A.n_groups == 4 ? 1 : 2)) : A.mode + 2;
     /* the fused LoRes4 kernel keeps the downsampled band inside the band buffer: launched without WarpSmem::lo */
-    const size_t smem1 = WARPS_PER_CTA == 1 && RENDER_INPLACE ? offsetof(WarpSmem, lo) + RENDER_EXTRA_SMEM : smem;
+    const size_t smem1 = RENDER_INPLACE ? offsetof(WarpSmem, lo) + RENDER_EXTRA_SMEM : smem;
     switch (variant) {
-    case 0: mg_render_kernel<0><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
-    case 1: mg_render_kernel<1><<<grid, WARPS_PER_CTA * 32, smem1, st>>>(S, A); break;
-    case 2: mg_render_kernel<2><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
-    case 3: mg_render_kernel<3><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
-    default: mg_render_kernel<4><<<grid, WARPS_PER_CTA * 32, smem, st>>>(S, A); break;
+    case 0: mg_render_kernel<0><<<grid, NT, smem, st>>>(S, A); break;
+    case 1: mg_render_kernel<1><<<grid, NT, smem1, st>>>(S, A); break;
+    case 2: mg_render_kernel<2><<<grid, NT, smem, st>>>(S, A); break;
+    case 3: mg_render_kernel<3><<<grid, NT, smem, st>>>(S, A); break;
+    default: mg_render_kernel<4><<<grid, NT, smem, st>>>(S, A); break;
     }
 }
 
