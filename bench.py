@@ -394,17 +394,43 @@ def run_gpu(args, rank, world, local_rank):
         env.step_host(a_host[t % T_act], obs_host, rew_host, done_host, score_host)
         state['t'] = t + 1
 
-    for _ in range(min(W, 3)):
-        host_step()
-    sync_all()
-    t0 = time.perf_counter()
-    for _ in range(Ke):
-        host_step()
-    torch.cuda.synchronize(dev)
-    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * Ke / float(e2e_s.item())
+    def time_host_steps(warm):
+        for _ in range(warm):
+            host_step()
+        sync_all()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            host_step()
+            if os.environ.get('MG_BENCH_DEBUG'):
+                print('e2e step', '%.3f' % ((time.perf_counter() - t0) * 1e3), env.host_assembly(), file=sys.stderr)
+        torch.cuda.synchronize(dev)
+        s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(s, op=dist.ReduceOp.MAX)
+        return world * B * Ke / float(s.item())
+
+    # (a) every stacked observation crosses the link whole (110 592 B per env-step)
+    e2e_direct = time_host_steps(min(W, 3))
+    obs_bytes_env = obs.numel() // B
+    e2e_value, e2e_d2h, e2e_mode = e2e_direct, world * (obs.numel() + B * 9), 'every stacked observation copied whole'
+    asm_info = None
+    if args.e2e_assembly != 'off':
+        # (b) mg_set_host_assembly: part of the batch sends only its new frame and host threads build those stacks
+        # (same bytes in obs_host); the handle balances link against host over the warm-up steps
+        local_world = int(os.environ.get('LOCAL_WORLD_SIZE', world))
+        threads = max(1, host_cores() // max(local_world, 1))
+        env.set_host_assembly('auto', 0, threads)
+        e2e_asm = time_host_steps(36)
+        parts, total, threads, copy_ms, asm_ms = env.host_assembly()
+        env.set_host_assembly('off')
+        asm_info = {'value': e2e_asm, 'parts_built_on_host': parts, 'parts': total, 'host_threads': threads,
+                    'last_step_copy_ms': copy_ms, 'last_step_host_ms': asm_ms}
+        if e2e_asm > e2e_direct:
+            n_asm_envs = B * parts // total
+            e2e_value = e2e_asm
+            e2e_d2h = world * (n_asm_envs * (obs_bytes_env // 4) + (B - n_asm_envs) * obs_bytes_env + B * 9)
+            e2e_mode = (f'mg_set_host_assembly(auto): {parts} of {total} parts of the batch send only their new 96x96x3 frame and '
+                        f'{threads} host threads build those stacked observations in the pinned output buffer')
     status = env.status()
     if rank == 0:
         peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
@@ -441,7 +467,9 @@ def run_gpu(args, rank, world, local_rank):
                          'note': 'frac: algorithmic bytes (110592 B x envs per launch) / render-kernel time; frac_step: SURVEY 8(d) / BASELINE.md 4 definition, env-steps/s per GPU x 110592 B / peak (whole step). The kernels are issue/latency-bound, not HBM-bound'},
             'cpu_baseline': cb,
             'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': world * B * 4,
-                    'd2h_bytes_per_step': world * (obs.numel() + B * 9), 'steps': Ke},
+                    'd2h_bytes_per_step': e2e_d2h, 'steps': Ke, 'how': e2e_mode,
+                    'direct': {'value': e2e_direct, 'd2h_bytes_per_step': world * (obs.numel() + B * 9)},
+                    'host_assembly': asm_info},
             'api': {'value': api_value, 'unit': UNIT, 'steps': Ka, 'call': 'BatchedMagicalEnv.step (auto_reset=True, device tensors)'},
             'gpu_launches': launches, 'host_issue_ms_per_step': host_ms,
             'clocks': clock_info,
@@ -461,6 +489,8 @@ def main():
     ap.add_argument('--workload', default='cfg1', choices=sorted(WORKLOADS))
     ap.add_argument('--envs', type=int, default=0, help='envs per GPU (default: the workload\'s)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--e2e-assembly', default='auto', choices=['auto', 'off'],
+                    help='end-to-end arm: also time mg_step_host with mg_set_host_assembly (new frame over the link, stacks built by host threads)')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))

@@ -127,6 +127,27 @@ int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream);
 int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *obs_host, float *reward_host,
                  uint8_t *done_host, float *score_host);
 
+/* Host assembly for mg_step_host.  What BaseEnv.step returns under the LoRes4* wrappers is the stack of the last four
+ * frames (FlattenFrameStack.step, magical/benchmarks/__init__.py:122-137), and three of the four are already on the host
+ * after the previous step.  With host assembly on, mg_step_host sends only the NEW 96x96x3 frame of the first `chunks`
+ * of its 16 parts of the batch over PCIe (27 648 B per env instead of 110 592 B) into a pinned mirror of the frame ring
+ * and `n_threads` host threads build those envs' stacked observations in obs_host while the other parts arrive as
+ * finished stacks: same bytes as before, more env-steps per second when the link is the limit and host cores are free.
+ * mode 0: off (default).  mode 1: the handle moves `chunks` step by step until link and host finish together (chunks
+ * = starting value, 0: half).  mode 2: `chunks` fixed.  n_threads <= 0: $MG_HOST_THREADS, else all hardware threads.
+ * Single-view HWC stacks only (MG_ERR_ARG otherwise).  Any render outside mg_step_host (mg_step, mg_step_render,
+ * mg_reset_obs, mg_set_state) makes the next mg_step_host refetch the whole ring of the assembled parts once. */
+int mg_set_host_assembly(mg_handle *h, int mode, int chunks, int n_threads);
+/* current number of host-assembled parts / parts in all / host threads, and the last step's device-side copy time and
+ * host-side assembly time in ms (any pointer may be NULL) */
+int mg_get_host_assembly(const mg_handle *h, int *chunks_out, int *total_chunks_out, int *threads_out,
+                         double *copy_ms_out, double *host_ms_out);
+/* The host half alone (FlattenFrameStack over frames the caller holds, magical/benchmarks/__init__.py:122-147):
+ * obs_host u8 [n_envs,96,96,3*n_groups], group g of env e = ring_host[e][(newest_slot - min(ages[g], since_reset[e])) & 3]
+ * with ring_host u8 [n_envs,4,96,96,3]; since_reset[e] = frames since the env's episode began (3 = at least three). */
+int mg_host_stack_frames(const uint8_t *ring_host, uint8_t *obs_host, int n_envs, int newest_slot,
+                         const int32_t *ages, int n_groups, const uint8_t *since_reset, int n_threads);
+
 /* Render one view of every env.  full_res != 0: out_dev u8 [B,384,384,3];
  * else the 4x area-averaged u8 [B,96,96,3].  Does not touch the frame stacks. */
 int mg_render(mg_handle *h, int view, int full_res, uint8_t *out_dev, void *stream);

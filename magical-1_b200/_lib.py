@@ -80,6 +80,10 @@ SYMBOLS = {
     'mg_step_physics': (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
     'mg_step_render': (C.c_int, [_VP, _VP, _VP]),
     'mg_step_host': (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP]),
+    'mg_set_host_assembly': (C.c_int, [_VP, C.c_int, C.c_int, C.c_int]),
+    'mg_get_host_assembly': (C.c_int, [_VP, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                       C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    'mg_host_stack_frames': (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP, C.c_int, _VP, C.c_int]),
     'mg_render': (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP]),
     'mg_score': (C.c_int, [_VP, _VP, _VP]),
     'mg_debug_reward': (C.c_int, [_VP, _VP, _VP]),

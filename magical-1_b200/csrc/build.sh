@@ -8,7 +8,7 @@ NVCC=${NVCC:-nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false -std=c++17 -Xcompiler -fPIC,-fno-fast-math,-ffp-contract=off"
 OBJ=${OBJ_DIR:-_obj}
 mkdir -p "$OBJ"
-SRCS="mg_physics.cu mg_raster.cu mg_api.cu mg_frames.cu mg_tables.cpp mg_reset.cpp"
+SRCS="mg_physics.cu mg_raster.cu mg_api.cu mg_frames.cu mg_tables.cpp mg_reset.cpp mg_hostasm.cpp"
 pids=""
 for f in $SRCS; do
     $NVCC $FLAGS "$@" -c -o "$OBJ/${f%.*}.o" "$f" &

@@ -12,10 +12,13 @@
 #include <vector>
 #include "mg_kernels.h"
 #include "mg_tables.h"
+#include "mg_hostasm.h"
+#include <chrono>
+#include <thread>
 #include "../../include/mg_trig.h"
 
 #define MG_STEP_PARTS 32   /* parts of the batch mg_step runs on their own streams */
-#define MG_HOST_CHUNKS 8   /* parts of the batch whose D2H copy overlaps the rendering of the next (mg_step_host) */
+#define MG_HOST_CHUNKS 16  /* parts of the batch whose D2H copy overlaps the rendering of the next (mg_step_host) */
 
 struct mg_handle {
     mg_config cfg;
@@ -46,6 +49,19 @@ struct mg_handle {
     int step_order;                          /* group the envs of a part by contact load (mg_order_kernel) */
     int *perm_dev;                           /* [B] env order of the current mg_step */
     cudaEvent_t chunk_done[MG_HOST_CHUNKS];
+    /* host-assembled part of mg_step_host (mg_set_host_assembly): chunks [0, asm_chunks) send only their NEW frame into a
+     * pinned mirror of the frame ring and the host builds their stacked observations (mg_hostasm.cpp) while the other
+     * chunks arrive as finished stacks */
+    int asm_mode;                            /* 0 off, 1 balanced by the handle, 2 fixed */
+    int asm_chunks;
+    uint8_t *ring_host;                      /* pinned [B][MG_MAX_RING][MG_FRAME_BYTES], lazily allocated */
+    uint8_t asm_hist_ok[MG_HOST_CHUNKS];     /* the mirror holds the chunk's three older frames */
+    std::vector<uint8_t> since_reset;        /* [B] frames since the env's episode began, saturating at MG_MAX_RING - 1 */
+    std::vector<int32_t> fresh_ids;          /* envs reset since the last mg_step_host */
+    MgHostAsm *hostasm;
+    cudaEvent_t chunk_copied[MG_HOST_CHUNKS], asm_t0, asm_t1;
+    int asm_hold;                            /* steps until the balance may move again */
+    double asm_last_copy_ms, asm_last_host_ms;
     /* last work this handle put on a CALLER's stream (mg_set_scenes, mg_reset_obs, mg_step*, mg_render): mg_step_host
      * runs on own_stream and must not start before it (the caller need not synchronise between the two) */
     cudaEvent_t caller_ev;
@@ -160,7 +176,15 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaMalloc(&h->done_dev, (size_t)B));
     CK(h, cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking));
     CK(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-    for (int c = 0; c < MG_HOST_CHUNKS; c++) CK(h, cudaEventCreateWithFlags(&h->chunk_done[c], cudaEventDisableTiming));
+    for (int c = 0; c < MG_HOST_CHUNKS; c++) {
+        CK(h, cudaEventCreateWithFlags(&h->chunk_done[c], cudaEventDisableTiming));
+        CK(h, cudaEventCreateWithFlags(&h->chunk_copied[c], cudaEventDisableTiming));
+        h->asm_hist_ok[c] = 0;
+    }
+    CK(h, cudaEventCreate(&h->asm_t0));
+    CK(h, cudaEventCreate(&h->asm_t1));
+    h->asm_mode = 0; h->asm_chunks = 0; h->ring_host = nullptr; h->hostasm = nullptr; h->asm_hold = 0;
+    h->asm_last_copy_ms = h->asm_last_host_ms = 0;
     for (int c = 0; c < MG_STEP_PARTS; c++) {
         CK(h, cudaStreamCreateWithFlags(&h->part_stream[c], cudaStreamNonBlocking));
         CK(h, cudaEventCreateWithFlags(&h->part_done[c], cudaEventDisableTiming));
@@ -195,7 +219,10 @@ extern "C" int mg_destroy(mg_handle *h)
     cudaFree(h->tables_dev); cudaFree(h->scene_stage_dev); cudaFree(h->ids_stage_dev);
     cudaFree(h->actions_dev); cudaFree(h->obs_dev); cudaFree(h->reward_dev); cudaFree(h->score_dev); cudaFree(h->done_dev);
     cudaStreamDestroy(h->own_stream); cudaStreamDestroy(h->copy_stream);
-    for (int c = 0; c < MG_HOST_CHUNKS; c++) cudaEventDestroy(h->chunk_done[c]);
+    for (int c = 0; c < MG_HOST_CHUNKS; c++) { cudaEventDestroy(h->chunk_done[c]); cudaEventDestroy(h->chunk_copied[c]); }
+    cudaEventDestroy(h->asm_t0); cudaEventDestroy(h->asm_t1);
+    if (h->ring_host) cudaFreeHost(h->ring_host);
+    mg_hostasm_destroy(h->hostasm);
     for (int c = 0; c < MG_STEP_PARTS; c++) { cudaStreamDestroy(h->part_stream[c]); cudaEventDestroy(h->part_done[c]); }
     cudaEventDestroy(h->fork_ev); cudaEventDestroy(h->caller_ev);
     for (int k = 0; k < 2; k++) { cudaFreeHost(h->scene_stage_host[k]); cudaFreeHost(h->ids_stage_host[k]); cudaEventDestroy(h->stage_ev[k]); }
@@ -212,6 +239,18 @@ static void mark_caller(mg_handle *h, cudaStream_t st)
 {
     if (st == h->own_stream) return;
     if (cudaEventRecord(h->caller_ev, st) == cudaSuccess) h->caller_ev_used = 1;
+}
+
+/* the frame rings moved without the host mirror seeing it (any render outside the host-assembled mg_step_host) */
+static void hostasm_invalidate(mg_handle *h)
+{
+    for (int c = 0; c < MG_HOST_CHUNKS; c++) h->asm_hist_ok[c] = 0;
+}
+/* envs whose next frame is the first of an episode */
+static void hostasm_note_resets(mg_handle *h, const int32_t *env_ids_host, int n)
+{
+    if (!h->asm_mode) return;
+    for (int i = 0; i < n; i++) h->fresh_ids.push_back(env_ids_host ? env_ids_host[i] : i);
 }
 
 static int check_launch(mg_handle *h, const char *what)
@@ -261,6 +300,7 @@ extern "C" int mg_set_scenes(mg_handle *h, const int32_t *env_ids_host, int n, c
     int rc = stage_upload(h, "mg_set_scenes", env_ids_host, n, scenes_host, st, &slot);
     if (rc != MG_OK) return rc;
     mg_launch_init(h->S, h->scene_stage_dev, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
+    hostasm_note_resets(h, env_ids_host, n);
     h->launches++;
     CK(h, cudaEventRecord(h->stage_ev[slot], st));
     h->stage_used[slot] = 1;
@@ -281,6 +321,7 @@ extern "C" int mg_queue_resets(mg_handle *h, const int32_t *env_ids_host, int n,
     int rc = stage_upload(h, "mg_queue_resets", env_ids_host, n, scenes_host, st, &slot);
     if (rc != MG_OK) return rc;
     mg_launch_mark_pending(h->S, env_ids_host ? h->ids_stage_dev : nullptr, n, st);
+    hostasm_note_resets(h, env_ids_host, n);
     h->launches++;
     /* the device staging is read by the step that applies the resets: its end is recorded by that step (pending_done) */
     h->pending_queued = 1 + slot;
@@ -341,6 +382,7 @@ extern "C" int mg_step_render(mg_handle *h, uint8_t *obs_dev, void *stream)
     if (!h) return fail(h, MG_ERR_ARG, "mg_step_render: bad argument");
     cudaStream_t st = (cudaStream_t)stream;
     CK(h, cudaSetDevice(h->cfg.device));
+    hostasm_invalidate(h);
     int last_view = -1;
     for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); last_view = v; }
     time_begin(h, 1, st);
@@ -410,6 +452,7 @@ static int step_in_parts(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_
                          float *score_dev, cudaStream_t st)
 {
     CK(h, cudaSetDevice(h->cfg.device));
+    hostasm_invalidate(h);
     int view = -1;
     for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) { h->slots[v] = (h->slots[v] + 1) & (MG_MAX_RING - 1); view = v; }
     static const bool debug_sync = getenv("MG_DEBUG_SYNC") && atoi(getenv("MG_DEBUG_SYNC")) != 0;
@@ -480,35 +523,126 @@ extern "C" int mg_step(mg_handle *h, const int32_t *actions_dev, uint8_t *obs_de
     return mg_step_render(h, obs_dev, stream);
 }
 
+/* ------------------------------------------------------------------ mg_step_host
+ * The end-to-end step.  The long pole is the observation's way to the host: 110 592 B per env over PCIe.  The batch is
+ * rendered in MG_HOST_CHUNKS parts and the device-to-host copy of each part starts as soon as it is rendered.  With
+ * host assembly on (mg_set_host_assembly), the first asm_chunks parts send only their NEW frame (a quarter of the bytes)
+ * into a pinned mirror of the frame ring and host threads build their stacks while the remaining parts arrive as
+ * finished stacks; the handle moves the boundary between the two sets until the link and the host finish together. */
+extern "C" int mg_set_host_assembly(mg_handle *h, int mode, int chunks, int n_threads)
+{
+    if (!h || mode < 0 || mode > 2 || chunks < 0 || chunks > MG_HOST_CHUNKS) return fail(h, MG_ERR_ARG, "mg_set_host_assembly: bad argument");
+    if (mode != 0 && !(h->fused && h->spec.n_groups > 0 && h->cfg.num_envs >= 4 * MG_HOST_CHUNKS))
+        return fail(h, MG_ERR_ARG, "mg_set_host_assembly: needs a single-view HWC frame stack and at least 64 envs");
+    CK(h, cudaSetDevice(h->cfg.device));
+    if (mode != 0) {
+        if (!h->ring_host) CK(h, cudaMallocHost(&h->ring_host, (size_t)h->cfg.num_envs * MG_MAX_RING * MG_FRAME_BYTES));
+        if (n_threads <= 0) {
+            const char *ev = getenv("MG_HOST_THREADS");
+            n_threads = ev ? atoi(ev) : (int)std::thread::hardware_concurrency();
+            if (n_threads <= 0) n_threads = 1;
+            if (n_threads > 64) n_threads = 64;
+        }
+        if (h->hostasm && mg_hostasm_threads(h->hostasm) != n_threads) { mg_hostasm_destroy(h->hostasm); h->hostasm = nullptr; }
+        if (!h->hostasm) h->hostasm = mg_hostasm_create(n_threads);
+        if (h->since_reset.empty()) h->since_reset.assign((size_t)h->cfg.num_envs, (uint8_t)(MG_MAX_RING - 1));
+    }
+    h->asm_mode = mode;
+    h->asm_chunks = mode == 0 ? 0 : (mode == 1 && chunks == 0 ? MG_HOST_CHUNKS / 2 : chunks);
+    h->asm_hold = 4;
+    h->fresh_ids.clear();
+    hostasm_invalidate(h);
+    return MG_OK;
+}
+
+extern "C" int mg_get_host_assembly(const mg_handle *h, int *chunks_out, int *total_chunks_out, int *threads_out,
+                                    double *copy_ms_out, double *host_ms_out)
+{
+    if (!h) return MG_ERR_ARG;
+    if (chunks_out) *chunks_out = h->asm_mode ? h->asm_chunks : 0;
+    if (total_chunks_out) *total_chunks_out = MG_HOST_CHUNKS;
+    if (threads_out) *threads_out = h->hostasm ? mg_hostasm_threads(h->hostasm) : 0;
+    if (copy_ms_out) *copy_ms_out = h->asm_last_copy_ms;
+    if (host_ms_out) *host_ms_out = h->asm_last_host_ms;
+    return MG_OK;
+}
+
+/* stacks from frames on the host, without a handle: what mg_step_host's workers do, for callers that keep their own
+ * frame history (and for the CPU-side test of the assembler) */
+extern "C" int mg_host_stack_frames(const uint8_t *ring_host, uint8_t *obs_host, int n_envs, int newest_slot,
+                                    const int32_t *ages, int n_groups, const uint8_t *since_reset, int n_threads)
+{
+    if (!ring_host || !obs_host || n_envs < 0 || !ages || n_groups < 1 || n_groups > MG_MAX_GROUPS || !since_reset)
+        return fail(nullptr, MG_ERR_ARG, "mg_host_stack_frames: bad argument");
+    for (int g = 0; g < n_groups; g++)
+        if (ages[g] < 0 || ages[g] >= MG_MAX_RING) return fail(nullptr, MG_ERR_ARG, "mg_host_stack_frames: bad age");
+    MgHostAsm *A = mg_hostasm_create(n_threads > 0 ? n_threads : 1);
+    int a[MG_MAX_GROUPS];
+    for (int g = 0; g < n_groups; g++) a[g] = ages[g];
+    mg_hostasm_begin(A, ring_host, obs_host, n_envs, newest_slot & (MG_MAX_RING - 1), a, n_groups, since_reset);
+    mg_hostasm_publish(A, n_envs);
+    mg_hostasm_finish(A);
+    mg_hostasm_destroy(A);
+    return MG_OK;
+}
+
 extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *obs_host, float *reward_host,
                             uint8_t *done_host, float *score_host)
 {
     if (!h || !actions_host) return fail(h, MG_ERR_ARG, "mg_step_host: bad argument");
+    const auto t_begin = std::chrono::steady_clock::now();
     const int B = h->cfg.num_envs;
     cudaStream_t st = h->own_stream;
     CK(h, cudaSetDevice(h->cfg.device));
     /* resets / renders the caller queued on its own stream (mg_set_scenes, mg_reset_obs, mg_step*) come first */
     if (h->caller_ev_used) { CK(h, cudaStreamWaitEvent(st, h->caller_ev, 0)); h->caller_ev_used = 0; }
+    const bool want_obs = obs_host && h->spec.n_groups > 0;
+    const bool chunked = h->fused && want_obs && B >= 4 * MG_HOST_CHUNKS;
+    int n_asm = chunked && h->asm_mode ? h->asm_chunks : 0, n_asm_envs = 0;
+    if (n_asm) CK(h, cudaEventRecord(h->asm_t0, st));       /* the device-side clock of the balance starts with the step */
     CK(h, cudaMemcpyAsync(h->actions_dev, actions_host, (size_t)B * sizeof(int32_t), cudaMemcpyHostToDevice, st));
     int rc = mg_step_physics(h, h->actions_dev, h->reward_dev, h->done_dev, h->score_dev, st);
     if (rc != MG_OK) return rc;
-    const bool want_obs = obs_host && h->spec.n_groups > 0;
-    if (h->fused && want_obs && B >= 4 * MG_HOST_CHUNKS) {
+    if (chunked) {
         /* single-view HWC stack: render the batch in MG_HOST_CHUNKS parts and start the device-to-host copy of
-         * each part as soon as it is rendered, so the PCIe transfer (the long pole: 110 KB per env) overlaps
-         * the rendering of the following parts */
+         * each part as soon as it is rendered, so the PCIe transfer overlaps the rendering of the following parts */
         int view = -1;
         for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) view = v;
         h->slots[view] = (h->slots[view] + 1) & (MG_MAX_RING - 1);
         const size_t env_bytes = h->obs_bytes / (size_t)B;
+        if (n_asm) for (int32_t id : h->fresh_ids) if (id >= 0 && id < B) h->since_reset[id] = 0;
+        h->fresh_ids.clear();
         for (int c = 0; c < MG_HOST_CHUNKS; c++) {
             const int e0 = (int)((long long)B * c / MG_HOST_CHUNKS), e1 = (int)((long long)B * (c + 1) / MG_HOST_CHUNKS);
-            mg_launch_render_push(h->S, view, h->slots[view], &h->spec, h->slots, h->obs_dev, e0, e1, st, h->pending_queued != 0);
+            const bool assembled = c < n_asm;
+            /* a host-assembled part only pushes its frame into the ring (no device-side stack) */
+            mg_launch_render_push(h->S, view, h->slots[view], assembled ? nullptr : &h->spec, h->slots, assembled ? nullptr : h->obs_dev,
+                                  e0, e1, st, h->pending_queued != 0);
             CK(h, cudaEventRecord(h->chunk_done[c], st));
             CK(h, cudaStreamWaitEvent(h->copy_stream, h->chunk_done[c], 0));
-            CK(h, cudaMemcpyAsync(obs_host + (size_t)e0 * env_bytes, h->obs_dev + (size_t)e0 * env_bytes,
-                                  (size_t)(e1 - e0) * env_bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+            if (assembled) {
+                const size_t env_ring = (size_t)MG_MAX_RING * MG_FRAME_BYTES;
+                if (h->asm_hist_ok[c]) {
+                    /* the mirror has the older frames: the new ring slot of every env of the part, 27 648 B each */
+                    const size_t off = (size_t)e0 * env_ring + (size_t)h->slots[view] * MG_FRAME_BYTES;
+                    CK(h, cudaMemcpy2DAsync(h->ring_host + off, env_ring, h->S.ring[view] + off, env_ring, MG_FRAME_BYTES,
+                                            (size_t)(e1 - e0), cudaMemcpyDeviceToHost, h->copy_stream));
+                } else {
+                    /* first time (or the rings moved behind the mirror's back): all four slots, as many bytes as the stacks */
+                    CK(h, cudaMemcpyAsync(h->ring_host + (size_t)e0 * env_ring, h->S.ring[view] + (size_t)e0 * env_ring,
+                                          (size_t)(e1 - e0) * env_ring, cudaMemcpyDeviceToHost, h->copy_stream));
+                    for (int e = e0; e < e1; e++) h->since_reset[e] = MG_MAX_RING - 1;     /* the device filled a fresh env's four slots */
+                    h->asm_hist_ok[c] = 1;
+                }
+                CK(h, cudaEventRecord(h->chunk_copied[c], h->copy_stream));
+                n_asm_envs = e1;
+            } else {
+                h->asm_hist_ok[c] = 0;
+                CK(h, cudaMemcpyAsync(obs_host + (size_t)e0 * env_bytes, h->obs_dev + (size_t)e0 * env_bytes,
+                                      (size_t)(e1 - e0) * env_bytes, cudaMemcpyDeviceToHost, h->copy_stream));
+            }
         }
+        if (n_asm) CK(h, cudaEventRecord(h->asm_t1, h->copy_stream));
         mg_launch_clear_fresh(h->S, st);
         h->launches += 2 * MG_HOST_CHUNKS + 1;
         rc = pending_done(h, st);
@@ -516,13 +650,40 @@ extern "C" int mg_step_host(mg_handle *h, const int32_t *actions_host, uint8_t *
         rc = check_launch(h, "mg_render_kernel");
         if (rc != MG_OK) return rc;
     } else {
-        rc = mg_step_render(h, h->obs_dev, st);
+        rc = mg_step_render(h, h->obs_dev, st);          /* invalidates the host mirror */
         if (rc != MG_OK) return rc;
+        h->fresh_ids.clear();
         if (want_obs) CK(h, cudaMemcpyAsync(obs_host, h->obs_dev, h->obs_bytes, cudaMemcpyDeviceToHost, st));
     }
     if (reward_host) CK(h, cudaMemcpyAsync(reward_host, h->reward_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
     if (done_host) CK(h, cudaMemcpyAsync(done_host, h->done_dev, (size_t)B, cudaMemcpyDeviceToHost, st));
     if (score_host) CK(h, cudaMemcpyAsync(score_host, h->score_dev, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (n_asm) {
+        /* build the stacks of the host-assembled parts as their frames land */
+        int view = -1;
+        for (int v = 0; v < 2; v++) if (h->spec.render_view[v]) view = v;
+        mg_hostasm_begin(h->hostasm, h->ring_host, obs_host, n_asm_envs, h->slots[view], h->spec.age, h->spec.n_groups, h->since_reset.data());
+        for (int c = 0; c < n_asm; c++) {
+            CK(h, cudaEventSynchronize(h->chunk_copied[c]));
+            mg_hostasm_publish(h->hostasm, (int)((long long)B * (c + 1) / MG_HOST_CHUNKS));
+        }
+        mg_hostasm_finish(h->hostasm);
+        const double host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+        for (int e = 0; e < B; e++) if (h->since_reset[e] < MG_MAX_RING - 1) h->since_reset[e]++;
+        CK(h, cudaStreamSynchronize(st));
+        CK(h, cudaStreamSynchronize(h->copy_stream));
+        float copy_ms = 0;
+        CK(h, cudaEventElapsedTime(&copy_ms, h->asm_t0, h->asm_t1));
+        h->asm_last_copy_ms = copy_ms; h->asm_last_host_ms = host_ms;
+        /* both clocks start when the first part begins to render (the host got here within microseconds of queueing it):
+         * move one part towards the side that finished first, with some hysteresis */
+        if (h->asm_mode == 1 && --h->asm_hold <= 0) {
+            const double slack = copy_ms - host_ms, tol = 0.04 * (copy_ms > host_ms ? copy_ms : host_ms) + 0.1;
+            if (slack > tol && h->asm_chunks < MG_HOST_CHUNKS) { h->asm_chunks++; h->asm_hold = 3; }
+            else if (slack < -tol && h->asm_chunks > 0) { h->asm_chunks--; h->asm_hold = 3; }
+        }
+        return MG_OK;
+    }
     CK(h, cudaStreamSynchronize(st));
     CK(h, cudaStreamSynchronize(h->copy_stream));
     return MG_OK;
@@ -653,7 +814,7 @@ extern "C" int mg_get_state(mg_handle *h, const int32_t *env_ids_host, int n, vo
 extern "C" int mg_set_state(mg_handle *h, const int32_t *env_ids_host, int n, const void *blobs_host)
 {
     /* restored envs may hold any number of blocks */
-    if (h) h->max_blocks = MG_MAX_BLOCKS;
+    if (h) { h->max_blocks = MG_MAX_BLOCKS; hostasm_invalidate(h); }
     return state_xfer(h, env_ids_host, n, (unsigned char *)blobs_host, true);
 }
 

@@ -479,6 +479,20 @@ class BatchedMagicalEnv:
         if len(finished):
             self._episode_steps[finished] = 0
 
+    def set_host_assembly(self, mode='auto', chunks=0, threads=0):
+        """mg_set_host_assembly: let step_host send only the NEW frame of part of the batch over PCIe and build those
+        envs' stacked observations with host threads (same bytes; single-view HWC stacks such as LoRes4E only).
+        mode: 'off', 'auto' (the handle balances link and host) or 'fixed' (`chunks` of the 16 parts)."""
+        m = {'off': 0, 'auto': 1, 'fixed': 2}[mode]
+        self._check(self._lib.mg_set_host_assembly(self._h, m, int(chunks), int(threads)))
+
+    def host_assembly(self):
+        """(host-assembled parts, parts, host threads, last step's copy ms, last step's host ms)"""
+        a, b, t = C.c_int(0), C.c_int(0), C.c_int(0)
+        cm, hm = C.c_double(0), C.c_double(0)
+        self._lib.mg_get_host_assembly(self._h, C.byref(a), C.byref(b), C.byref(t), C.byref(cm), C.byref(hm))
+        return a.value, b.value, t.value, cm.value, hm.value
+
     def set_timing(self, enable):
         self._check(self._lib.mg_set_timing(self._h, int(enable)))
 
