@@ -418,7 +418,7 @@ def run_gpu(args, rank, world, local_rank):
         # (b) mg_set_host_assembly: part of the batch sends only its new frame and host threads build those stacks
         # (same bytes in obs_host); the handle balances link against host over the warm-up steps
         local_world = int(os.environ.get('LOCAL_WORLD_SIZE', world))
-        threads = max(1, host_cores() // max(local_world, 1))
+        threads = int(os.environ.get('MG_BENCH_E2E_THREADS', 0)) or max(1, host_cores() // max(local_world, 1))
         env.set_host_assembly('auto', 0, threads)
         e2e_asm = time_host_steps(36)
         parts, total, threads, copy_ms, asm_ms = env.host_assembly()

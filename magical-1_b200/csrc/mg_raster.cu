@@ -639,11 +639,9 @@ __global__ void __launch_bounds__(NT, RENDER_MIN_CTAS) mg_render_kernel(MgDevice
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t pal[32];
     const MgTables *T = S.tables;
-    if (threadIdx.x < 32) {
-        const uint8_t *p = T->pal[threadIdx.x];
-        pal[threadIdx.x] = p[0] | (p[1] << 8) | (p[2] << 16);
-    }
-    __syncthreads();
+    /* r | g << 8 | b << 16 (MgTables::pal rows are r g b 0); first read after the barrier that follows the background fill */
+    static_assert(offsetof(MgTables, pal) % 4 == 0, "palette rows load as words");
+    if (threadIdx.x < 32) pal[threadIdx.x] = ((const uint32_t *)T->pal)[threadIdx.x];
     /* one band per CTA; its NT threads: tid spreads data-parallel work, lane / wid matter where a warp acts as one */
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     int env = A.env_begin + (int)(blockIdx.x / N_BANDS);
@@ -670,10 +668,14 @@ __global__ void __launch_bounds__(NT, RENDER_MIN_CTAS) mg_render_kernel(MgDevice
     const MgScreenPrim *sprims = S.sprims[A.view] + (size_t)env * MG_MAX_PRIMS;
     const int2 *sverts = S.sverts[A.view] + (size_t)env * MG_MAX_VERTS;
     const int np = S.n_prims[env];
+    /* needed after the painting (does the env start an episode with this frame?): asked for now, so that the answer has
+     * long arrived by then */
+    int fresh_word = 0;
+    if (MODE == 0) fresh_word = S.istate[mg_field_index(env, I_NF, I_FRESH)];
     /* the first 32 headers are on their way while the background is filled */
     const MgScreenPrim no_prim = { 0, 0x7fffffff, -0x7fffffff - 1, 0 };
-    MgScreenPrim first = no_prim;
-    if (lane < np) first = sprims[lane];
+    MgScreenPrim first = sprims[lane];            /* MG_MAX_PRIMS >= 32 entries exist; the load does not wait for np */
+    if (lane >= np) first = no_prim;
     /* Viewer._clear: background */
     {
         const uint32_t bg4 = MG_PAL_BG * 0x01010101u;
@@ -809,7 +811,7 @@ __global__ void __launch_bounds__(NT, RENDER_MIN_CTAS) mg_render_kernel(MgDevice
     constexpr int PRE_IT = LO_ROWS * MG_LORES / 4 / NT;
     uint32_t pre[VARIANT == 1 ? PRE_IT : 1][3][3];
     bool fresh = false, use_pre = false;
-    if (MODE == 0) fresh = S.istate[mg_field_index(env, I_NF, I_FRESH)] != 0;
+    if (MODE == 0) fresh = fresh_word != 0;
     if (VARIANT == 1) {
         use_pre = !fresh && A.gview[3] == A.view && A.gage[3] == 0;
 #pragma unroll
