@@ -688,6 +688,9 @@ extern "C" int mg_debug_read_timers(long long *out_host, int n_ctas)
 #define TM_ADD(k_)
 #endif
 
+#ifndef PHYS_LEAD_ROTATE
+#define PHYS_LEAD_ROTATE 1
+#endif
 #define NARROW_SLOTS 1
 /* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
 struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
@@ -1575,7 +1578,24 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     TM_DECL(tm_cta);
     const EnvRef g = env_ref(S.dstate, S.istate, env);
     PhysSmemFixed *W = &sm[grp];
+    /* Which warp leads (runs the CTA's serial chains).  The CTAs resident on one SM occupy hardware warp slots a
+     * multiple of the CTA's warp count apart, and a slot's scheduler is slot % 4: with warp 0 leading everywhere, the
+     * lead warps of an SM's CTAs would all sit on one scheduler and share its FP64 pipe (one DADD per 2.3 cycles and
+     * warp) while the other three idle through the serial half.  The CTA in slot group k leads with the warp whose
+     * slot is k mod 4 instead. */
+    __shared__ int lead_warp_sh;
+#if PHYS_LEAD_ROTATE && !defined(MG_SECTION_TIMERS)
+    if (threadIdx.x == 0) {
+        unsigned hw;
+        asm volatile("mov.u32 %0, %%warpid;" : "=r"(hw));
+        lead_warp_sh = (int)(((hw / (PHYS_THREADS_T / 32)) - hw) & 3);
+    }
+#else
+    if (threadIdx.x == 0) lead_warp_sh = 0;       /* the section timers live on thread 0 */
+#endif
     __syncthreads();
+    const int warp = threadIdx.x >> 5, lead_warp = lead_warp_sh;
+    const bool is_lead = warp == lead_warp;
     double *Wd = smd + (size_t)grp * nd;
 
     /* stage the env: ints first (they hold the counts), then the bodies and constraints in use */
@@ -1593,13 +1613,13 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     e.ap = Wd + pool_off; e.ainfo = W->ainfo; e.apn = pool_n;
     /* lane k of warp 0 runs the robot chain and the contacts of env k of this CTA (solve_lead): it needs that env's
      * arbiter cache in HBM */
-    const bool solver = threadIdx.x < ENVS && env0 + lane < S.num_envs;
+    const bool solver = is_lead && lane < ENVS && env0 + lane < S.num_envs;
     EnvRef gs = g;
     if (solver) gs = env_ref(S.dstate, S.istate, PERM ? S.perm[env0 + lane] : env0 + lane);
     /* the other warps: lane = (env k of the CTA, block hb of that env) runs that block's floor-friction pair */
     constexpr int SLOTS_PER_WARP = 32 / ENVS;
     static_assert((PHYS_THREADS_T / 32 - 1) * SLOTS_PER_WARP >= MG_MAX_BLOCKS, "a helper lane per block");
-    const int hk = lane % ENVS, hb = (threadIdx.x / 32 - 1) * SLOTS_PER_WARP + lane / ENVS;
+    const int hk = lane % ENVS, hb = (warp - (warp > lead_warp ? 1 : 0)) * SLOTS_PER_WARP + lane / ENVS;   /* helper warps count past the lead */
     EnvRef eh = e;
     eh.d = smd + (size_t)hk * nd; eh.dc = eh.d + con_off; eh.i = sm[hk].i;
     bool helper = false;          /* known once the env is staged (block count) */
@@ -1616,7 +1636,7 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
     double target_finger_angle = grip == 0 ? M_PI / 8 : -0.0;
 
     __syncthreads();              /* every env of the CTA is staged: the helper lanes read another group's counters */
-    helper = threadIdx.x >= 32 && env0 + hk < S.num_envs && hb < IF(eh, I_NBLOCKS);
+    helper = !is_lead && env0 + hk < S.num_envs && hb < IF(eh, I_NBLOCKS);
     TM_ADD(TM_STAGE);
     const int rb = MG_BODY_ROBOT;
     const int motor_l = active ? (IF(e, I_ROBOT_FIRST) ? 6 : 2 * IF(e, I_NBLOCKS) + 6) : 0;  /* robot constraints 0..9: motors are 6 and 9 */
@@ -1651,7 +1671,7 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
         TM_ADD(TM_PARALLEL);
         const int any_live = __syncthreads_or(n_live_sub != 0);
         TM_ADD(TM_BARRIER);
-        if (threadIdx.x < 32) solve_lead<ENVS>(solver, lane & (ENVS - 1), max_blocks, pool_n, gs.da, gs.ia, any_live, tm_cta);
+        if (is_lead) solve_lead<ENVS>(solver, lane & (ENVS - 1), max_blocks, pool_n, gs.da, gs.ia, any_live, tm_cta);
         else solve_helper<ENVS>(helper, hk, hb, max_blocks, pool_n, any_live);
         TM_ADD(TM_SERIAL);
         __syncthreads();

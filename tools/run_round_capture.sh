@@ -8,8 +8,10 @@ python bench.py > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err
 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > $O/${TAG}_bench_driver_window.json 2>> $O/${TAG}_bench.err
 for w in cfg2 cfg3 cfg5; do python bench.py --workload $w --steps 40 --warmup 5 > $O/${TAG}_bench_$w.json 2>> $O/${TAG}_bench.err; done
 python bench.py --impl reference --steps 3 --warmup 1 > $O/${TAG}_bench_ref.json 2>> $O/${TAG}_bench.err
-tools/ubench/host_shift 4096 16 > $O/${TAG}_host_shift.txt 2>&1; tools/ubench/host_shift 4096 32 >> $O/${TAG}_host_shift.txt 2>&1
-tools/ubench/lat > $O/${TAG}_fp64_latency.txt 2>&1; tools/ubench/fp64tp >> $O/${TAG}_fp64_latency.txt 2>&1
+[ -x tools/ubench/host_shift ] && { tools/ubench/host_shift 4096 16 > $O/${TAG}_host_shift.txt 2>&1; tools/ubench/host_shift 4096 32 >> $O/${TAG}_host_shift.txt 2>&1; }
+[ -x tools/ubench/lat ] && { tools/ubench/lat > $O/${TAG}_fp64_latency.txt 2>&1; tools/ubench/fp64tp >> $O/${TAG}_fp64_latency.txt 2>&1; }
+# end-to-end step with host assembly: fixed splits and the handle's own balance (tools/time_e2e.py)
+python tools/time_e2e.py 4096 > $O/${TAG}_e2e_host_assembly.txt 2>&1
 # launch list of the step as the bench runs it (one graph replay per step: order + 16 x (physics, geometry, raster) + clear)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_graph.csv \
     python bench.py --steps 6 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu_launch_graph.log 2>&1
