@@ -177,7 +177,12 @@ struct MgHostAsm {
         for (;;) {
             const int i = next.fetch_add(1, std::memory_order_acq_rel);
             if (i >= n_envs) return;
-            while (i >= limit.load(std::memory_order_acquire)) std::this_thread::yield();
+            if (i >= limit.load(std::memory_order_acquire)) {
+                /* its frame has not landed: sleep until the next publish (no spinning: the cores belong to whoever
+                 * else runs on the host, e.g. the thread that samples the coming episodes) */
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return i < limit.load(std::memory_order_acquire); });
+            }
             one_env(i);
             done.fetch_add(1, std::memory_order_release);
         }
@@ -233,12 +238,16 @@ void mg_hostasm_begin(MgHostAsm *A, const uint8_t *ring_host, uint8_t *obs_host,
     A->cv.notify_all();
 }
 
-void mg_hostasm_publish(MgHostAsm *A, int env_limit) { A->limit.store(env_limit, std::memory_order_release); }
+void mg_hostasm_publish(MgHostAsm *A, int env_limit)
+{
+    { std::lock_guard<std::mutex> lk(A->mu); A->limit.store(env_limit, std::memory_order_release); }
+    A->cv.notify_all();
+}
 
 void mg_hostasm_finish(MgHostAsm *A)
 {
     A->work();
-    while (A->done.load(std::memory_order_acquire) < A->n_envs) std::this_thread::yield();
+    while (A->done.load(std::memory_order_acquire) < A->n_envs) std::this_thread::yield();     /* the last few envs in flight */
 }
 
 int mg_hostasm_threads(const MgHostAsm *A) { return (int)A->threads.size() + 1; }
