@@ -1756,8 +1756,22 @@ __global__ void __launch_bounds__(1024) mg_order_kernel(MgDeviceState S, int *pe
     __shared__ int class_base[5];
     const int B = S.num_envs, t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int per = (B + 1023) / 1024, e0 = t * per, e1 = min(B, e0 + per);
+    /* the kernel is one CTA on the step's critical path and its time is the latency of these loads: up to KEYS envs per
+     * thread are read once, all loads in flight together, and kept in registers for the scatter pass */
+    constexpr int KEYS = 8;
+    int key[KEYS];
+    const bool in_regs = per <= KEYS;
+    if (in_regs) {
+#pragma unroll
+        for (int j = 0; j < KEYS; j++) key[j] = e0 + j < e1 ? S.istate[mg_field_index(e0 + j, I_NF, I_NARBS)] : 0;
+    }
     int cnt[4] = { 0, 0, 0, 0 };
-    for (int env = e0; env < e1; env++) cnt[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++;
+    if (in_regs) {
+#pragma unroll
+        for (int j = 0; j < KEYS; j++) if (e0 + j < e1) cnt[min(key[j], 3)]++;
+    } else {
+        for (int env = e0; env < e1; env++) cnt[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++;
+    }
     int pos[4];
     if (t == 0) class_base[0] = 0;
     for (int c = 0; c < 4; c++) {
@@ -1775,7 +1789,12 @@ __global__ void __launch_bounds__(1024) mg_order_kernel(MgDeviceState S, int *pe
         pos[c] = class_base[c] + warp_sum[warp] + incl - v;
         __syncthreads();
     }
-    for (int env = e0; env < e1; env++) perm[pos[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++] = env;
+    if (in_regs) {
+#pragma unroll
+        for (int j = 0; j < KEYS; j++) if (e0 + j < e1) perm[pos[min(key[j], 3)]++] = e0 + j;
+    } else {
+        for (int env = e0; env < e1; env++) perm[pos[min(S.istate[mg_field_index(env, I_NF, I_NARBS)], 3)]++] = env;
+    }
 }
 
 void mg_launch_order(const MgDeviceState &S, int *perm, cudaStream_t st)

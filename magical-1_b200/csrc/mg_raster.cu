@@ -531,15 +531,28 @@ struct RenderArgs {
 };
 
 /* ---------------------------------------------------------------- geometry pass
- * One warp per env: walks the env's draw list once per view, builds each primitive's transform chain
- * (Viewer.render -> Geom.render -> stack.apply_current_matrix, render.py:116-160, 373-392), transforms the
- * vertices in FP64 and truncates them the way pygame converts its float arguments to int.  The band
- * rasterisers then only see integers. */
-__global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int view, int env_begin, int env_end, int apply_pending)
+ * One warp per env: builds each primitive's transform chain (Viewer.render -> Geom.render ->
+ * stack.apply_current_matrix, render.py:116-160, 373-392), transforms the vertices in FP64 and truncates them the way
+ * pygame converts its float arguments to int.  The band rasterisers then only see integers.
+ * The kernel sits between an env's physics and its raster on the step's critical path, so it is laid out for latency:
+ * lane = primitive for the transform chains (32 chains side by side instead of one after the other), then lane = vertex
+ * over the chunk's vertices in one flat loop (the owning primitive found by a search of the chunk's prefix sums), row and
+ * column extents by shared-memory atomics.  Every vertex is the same arithmetic as in a serial walk of the draw list. */
+#define GEO_WARPS 4
+struct GeoChunk {                       /* one chunk of 32 primitives of one env */
+    aff M[32];
+    double gw[32], gh[32];              /* goal regions: width and height (their vertices are made here) */
+    int pre[33];                        /* exclusive prefix sums of the vertex counts */
+    int ext[32][4];                     /* miny, maxy, minx, maxx */
+    MgPrim P[32];
+};
+__global__ void __launch_bounds__(GEO_WARPS * 32) mg_geometry_kernel(MgDeviceState S, int view, int env_begin, int env_end, int apply_pending)
 {
+    __shared__ GeoChunk chunks[GEO_WARPS];
     const MgTables *T = S.tables;
     const int lane = threadIdx.x & 31;
-    const int slot = env_begin + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    GeoChunk *C = &chunks[threadIdx.x >> 5];
+    const int slot = env_begin + blockIdx.x * GEO_WARPS + (threadIdx.x >> 5);
     if (slot >= env_end) return;
     const int env = S.perm ? S.perm[slot] : slot;
     /* a reset queued for this env (mg_queue_resets): this step's physics is done with the old episode (stream order),
@@ -560,72 +573,117 @@ __global__ void __launch_bounds__(128) mg_geometry_kernel(MgDeviceState S, int v
     int2 *sverts = S.sverts[view] + (size_t)env * MG_MAX_VERTS;
     double *dashv = S.dashv[view] + (size_t)env * MG_MAX_GOALS * 8;
     const int np = S.n_prims[env];
-    int off = 0;
-    for (int pi = 0; pi < np; pi++) {
-        const MgPrim P = prims[pi];
-        aff M;
-        const vec2 *lv = T->dl_pool + T->dl_off[P.dl];
-        int n = T->dl_n[P.dl];
-        double gw = 0, gh = 0;
-        switch (P.chain) {
-        case MG_CHAIN_CAM: M = cam; break;
-        case MG_CHAIN_BODY: {
-            const double *b = pose + P.body * MG_POSE_NF;
-            M = P.body == MG_BODY_ROBOT ? cam_robot : aff_mul(cam, aff_tr(b[0], b[1], b[6], b[7]));
-            break;
-        }
-        case MG_CHAIN_EYE:
-        case MG_CHAIN_PUPIL: {
-            const double radius = 0.2;
-            double x_sign = P.aux == 0 ? -1.0 : 1.0;
-            M = aff_mul(cam_robot, aff_tr(x_sign * 0.4 * radius, 0.3 * radius, 1.0, 0.0));
-            if (P.chain == MG_CHAIN_PUPIL) {
-                double rel = pose[P.body * MG_POSE_NF + 2] - rp[2];   /* pupil.angle - robot.angle, entities.py:489-491 */
-                double sn, cs;
-                mg_sincos(rel, &sn, &cs);
-                M = aff_mul(M, aff_tr(0.0, 0.0, cs, sn));
-                M = aff_mul(M, aff_tr(0.0, radius * 0.07, 1.0, 0.0));
+    int off = 0;                        /* first vertex of the chunk in the env's pool: every primitive keeps its place,
+                                         * visible or not (the pool holds the largest scene's whole draw list) */
+    for (int base = 0; base < np; base += 32) {
+        const int pi = base + lane;
+        /* lane = primitive: its transform chain */
+        int n = 0;
+        MgPrim P = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        if (pi < np) {
+            P = prims[pi];
+            n = T->dl_n[P.dl];
+            aff M;
+            double gw = 0, gh = 0;
+            switch (P.chain) {
+            case MG_CHAIN_CAM: M = cam; break;
+            case MG_CHAIN_BODY: {
+                const double *b = pose + P.body * MG_POSE_NF;
+                M = P.body == MG_BODY_ROBOT ? cam_robot : aff_mul(cam, aff_tr(b[0], b[1], b[6], b[7]));
+                break;
             }
-            break;
+            case MG_CHAIN_EYE:
+            case MG_CHAIN_PUPIL: {
+                const double radius = 0.2;
+                double x_sign = P.aux == 0 ? -1.0 : 1.0;
+                M = aff_mul(cam_robot, aff_tr(x_sign * 0.4 * radius, 0.3 * radius, 1.0, 0.0));
+                if (P.chain == MG_CHAIN_PUPIL) {
+                    double rel = pose[P.body * MG_POSE_NF + 2] - rp[2];   /* pupil.angle - robot.angle, entities.py:489-491 */
+                    double sn, cs;
+                    mg_sincos(rel, &sn, &cs);
+                    M = aff_mul(M, aff_tr(0.0, 0.0, cs, sn));
+                    M = aff_mul(M, aff_tr(0.0, radius * 0.07, 1.0, 0.0));
+                }
+                break;
+            }
+            default: { /* MG_CHAIN_GOAL */
+                const mg_goal *g = &S.scenes[env].goals[P.aux];
+                M = aff_mul(cam, aff_tr(g->cx, g->cy, 1.0, 0.0));
+                gw = g->w; gh = g->h;
+                break;
+            }
+            }
+            C->M[lane] = M; C->gw[lane] = gw; C->gh[lane] = gh; C->P[lane] = P;
         }
-        default: { /* MG_CHAIN_GOAL */
-            const mg_goal *g = &S.scenes[env].goals[P.aux];
-            M = aff_mul(cam, aff_tr(g->cx, g->cy, 1.0, 0.0));
-            gw = g->w; gh = g->h;
-            break;
+        /* the chunk's vertex ranges */
+        int incl = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += o; }
+        int total = __shfl_sync(FULL, incl, 31);
+        if (off + total > MG_MAX_VERTS) { n = 0; incl = 0; total = 0; }      /* cannot happen for scenes mg_set_scenes accepts */
+        C->pre[lane] = incl - n;
+        if (lane == 31) C->pre[32] = total;
+        C->ext[lane][0] = 0x7fffffff; C->ext[lane][1] = -0x7fffffff - 1; C->ext[lane][2] = 0x7fffffff; C->ext[lane][3] = -0x7fffffff - 1;
+        __syncwarp();
+        /* lane = vertex over the whole chunk: transform + truncate (stack.apply_current_matrix, then pygame's int
+         * conversion) */
+        {
+            /* a lane's vertices v, v + 32, ... stay with one primitive for a while (circles have 100): its matrix and
+             * style stay in registers and its extents are merged into shared memory only when the lane moves on */
+            int q = -1, q_end = 0, q_pre = 0;
+            aff M = cam;
+            MgPrim Pq = { 0, 0, 0, 0, 0, 0, 0, 0 };
+            const vec2 *lv = nullptr;
+            double rw = 0, rh = 0;
+            int y_lo = 0x7fffffff, y_hi = -0x7fffffff - 1, x_lo = 0x7fffffff, x_hi = -0x7fffffff - 1;
+            for (int v = lane; v < total; v += 32) {
+                if (v >= q_end) {
+                    if (q >= 0) {
+                        atomicMin(&C->ext[q][0], y_lo); atomicMax(&C->ext[q][1], y_hi);
+                        atomicMin(&C->ext[q][2], x_lo); atomicMax(&C->ext[q][3], x_hi);
+                    }
+                    q = 0;              /* last primitive whose range starts at or before v */
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) if (C->pre[q + d] <= v) q += d;
+                    q_pre = C->pre[q]; q_end = C->pre[q + 1];
+                    Pq = C->P[q]; M = C->M[q];
+                    lv = T->dl_pool + T->dl_off[Pq.dl];
+                    rw = C->gw[q] / 2; rh = C->gh[q] / 2;
+                    y_lo = x_lo = 0x7fffffff; y_hi = x_hi = -0x7fffffff - 1;
+                }
+                const int i = v - q_pre;
+                double x, y;
+                if (Pq.chain == MG_CHAIN_GOAL) {
+                    x = (i == 0 || i == 3) ? -rw : rw;
+                    y = (i < 2) ? rh : -rh;
+                } else { x = lv[i].x; y = lv[i].y; }
+                const double fx = (M.a * x + M.b * y) + M.tx;
+                const double fy = (M.c * x + M.d * y) + M.ty;
+                const int ix = (int)fx, iy = (int)fy;
+                sverts[off + v] = make_int2(ix, iy);
+                if (Pq.mode == 2 && i < 4) { dashv[Pq.aux * 8 + 2 * i] = fx; dashv[Pq.aux * 8 + 2 * i + 1] = fy; }
+                y_lo = min(y_lo, iy); y_hi = max(y_hi, iy); x_lo = min(x_lo, ix); x_hi = max(x_hi, ix);
+            }
+            if (q >= 0) {
+                atomicMin(&C->ext[q][0], y_lo); atomicMax(&C->ext[q][1], y_hi);
+                atomicMin(&C->ext[q][2], x_lo); atomicMax(&C->ext[q][3], x_hi);
+            }
         }
-        }
-        if (off + n > MG_MAX_VERTS) n = 0;      /* cannot happen for scenes mg_set_scenes accepts */
-        /* transform + truncate vertices (stack.apply_current_matrix, then pygame's int conversion) */
-        int miny = 0x7fffffff, maxy = -0x7fffffff - 1, minx = 0x7fffffff, maxx = -0x7fffffff - 1;
-        for (int i = lane; i < n; i += 32) {
-            double x, y;
-            if (P.chain == MG_CHAIN_GOAL) {
-                double rw = gw / 2, rh = gh / 2;
-                x = (i == 0 || i == 3) ? -rw : rw;
-                y = (i < 2) ? rh : -rh;
-            } else { x = lv[i].x; y = lv[i].y; }
-            double fx = (M.a * x + M.b * y) + M.tx;
-            double fy = (M.c * x + M.d * y) + M.ty;
-            int ix = (int)fx, iy = (int)fy;
-            sverts[off + i] = make_int2(ix, iy);
-            if (P.mode == 2 && i < 4) { dashv[P.aux * 8 + 2 * i] = fx; dashv[P.aux * 8 + 2 * i + 1] = fy; }
-            miny = min(miny, iy); maxy = max(maxy, iy);
-            minx = min(minx, ix); maxx = max(maxx, ix);
-        }
-        miny = __reduce_min_sync(FULL, miny); maxy = __reduce_max_sync(FULL, maxy);
-        minx = __reduce_min_sync(FULL, minx); maxx = __reduce_max_sync(FULL, maxx);
-        /* nothing of a primitive whose vertices all lie more than 4 pixels outside the surface can reach it
-         * (fills are clipped per row, outline copies are shifted by at most 2 and clipped) */
-        bool visible = n > 0 && maxy >= -4 && miny <= RES + 3 && maxx >= -4 && minx <= RES + 3;
-        if (lane == 0) {
+        __syncwarp();
+        /* lane = primitive again: the header the bands read */
+        if (pi < np) {
+            const int miny = C->ext[lane][0], maxy = C->ext[lane][1], minx = C->ext[lane][2], maxx = C->ext[lane][3];
+            /* nothing of a primitive whose vertices all lie more than 4 pixels outside the surface can reach it
+             * (fills are clipped per row, outline copies are shifted by at most 2 and clipped) */
+            const bool visible = n > 0 && maxy >= -4 && miny <= RES + 3 && maxx >= -4 && minx <= RES + 3;
             MgScreenPrim sp;
-            sp.off_n = visible ? (off << 8 | n) : 0;
+            sp.off_n = visible ? ((off + C->pre[lane]) << 8 | n) : 0;
             sp.miny = miny; sp.maxy = maxy;
             sp.style = (uint32_t)P.fill | (uint32_t)P.outline << 8 | (uint32_t)P.mode << 16 | (uint32_t)P.aux << 24;
             sprims[pi] = sp;
         }
-        if (visible) off += n;
+        off += total;
+        __syncwarp();                   /* the chunk's scratch is reused */
     }
 }
 
@@ -1072,7 +1130,7 @@ __global__ void mg_clear_fresh_kernel(MgDeviceState S)
 void mg_launch_geometry(const MgDeviceState &S, int view, int env_begin, int env_end, cudaStream_t st, int apply_pending)
 {
     if (env_end <= env_begin) return;
-    mg_geometry_kernel<<<(env_end - env_begin + 3) / 4, 128, 0, st>>>(S, view, env_begin, env_end, apply_pending);
+    mg_geometry_kernel<<<(env_end - env_begin + GEO_WARPS - 1) / GEO_WARPS, GEO_WARPS * 32, 0, st>>>(S, view, env_begin, env_end, apply_pending);
 }
 
 static void launch_render(const MgDeviceState &S, const RenderArgs &A, cudaStream_t st, int apply_pending = 0)
