@@ -71,3 +71,30 @@ def test_host_assembly_needs_a_single_view_stack():
     with pytest.raises(L.MgError):
         small.set_host_assembly('auto')
     small.close()
+
+
+def test_host_assembly_ragged_batch_and_restored_state():
+    """A batch that does not divide into the 16 parts evenly, and mg_set_state between two host-assembled steps (the
+    restored rings are not what the host mirror holds: the handle refetches them)."""
+    import torch
+    import magical_b200 as m
+    n = 100
+    a = m.make('MoveToCorner-Demo-LoRes4E-v0', num_envs=n, seed=3, obs_keys=('past_obs',))
+    b = m.make('MoveToCorner-Demo-LoRes4E-v0', num_envs=n, seed=3, obs_keys=('past_obs',))
+    a.auto_reset = b.auto_reset = False
+    a.reset(); b.reset()
+    a.set_host_assembly('fixed', 9, 2)
+    obs_h, rew_h, done_h, score_h, act_h = _pinned(n)
+    rs = np.random.RandomState(8)
+    saved = None
+    for t in range(12):
+        acts = rs.randint(0, 18, size=n)
+        act_h.copy_(torch.from_numpy(acts.astype(np.int32)))
+        if t == 4:
+            saved = (a.get_state(), b.get_state())
+        if t == 8:
+            a.set_state(saved[0]); b.set_state(saved[1])       # back to step 4: rings and poses of that time
+        a.step_host(act_h, obs_h, rew_h, done_h, score_h)
+        want = b.step(acts)[0]['past_obs'].cpu().numpy()
+        np.testing.assert_array_equal(obs_h.numpy(), want)
+    a.close(); b.close()
