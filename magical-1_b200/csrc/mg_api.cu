@@ -17,7 +17,7 @@
 #include <thread>
 #include "../../include/mg_trig.h"
 
-#define MG_STEP_PARTS 32   /* parts of the batch mg_step runs on their own streams */
+#define MG_STEP_PARTS 128  /* parts of the batch mg_step runs on their own streams */
 #define MG_HOST_CHUNKS 16  /* parts of the batch whose D2H copy overlaps the rendering of the next (mg_step_host) */
 
 struct mg_handle {
@@ -193,10 +193,12 @@ extern "C" int mg_create(const mg_config *cfg, mg_handle **out)
     CK(h, cudaEventCreateWithFlags(&h->caller_ev, cudaEventDisableTiming));
     h->caller_ev_used = 0;
     {
-        /* 16 parts of >= 256 envs measured best at 4096 envs (0.94 -> 0.87 ms); MG_STEP_PARTS=1 keeps the plain sequence */
+        /* parts of >= 128 envs, 32 at most, measured best at 4096 envs (plain sequence 0.80 ms, 16 parts 0.707, 32 parts
+         * 0.693, 64 parts 0.705); batches beyond 8192 envs (several waves of physics CTAs) are level from 8 to 32 parts
+         * and keep 16.  MG_STEP_PARTS=1 keeps the plain sequence */
         const char *ev = getenv("MG_STEP_PARTS");
-        h->step_parts = ev ? atoi(ev) : cfg->num_envs / 256;
-        if (!ev && h->step_parts > 16) h->step_parts = 16;
+        h->step_parts = ev ? atoi(ev) : (cfg->num_envs <= 8192 ? cfg->num_envs / 128 : 16);
+        if (!ev && h->step_parts > 32) h->step_parts = 32;
         if (h->step_parts > MG_STEP_PARTS) h->step_parts = MG_STEP_PARTS;
         const char *eg = getenv("MG_STEP_GRAPH");
         h->step_graph = eg ? atoi(eg) : 1;
