@@ -17,7 +17,7 @@
 #include <thread>
 #include "../../include/mg_trig.h"
 
-#define MG_STEP_PARTS 128  /* parts of the batch mg_step runs on their own streams */
+#define MG_STEP_PARTS 64   /* parts of the batch mg_step runs on their own streams */
 #define MG_HOST_CHUNKS 16  /* parts of the batch whose D2H copy overlaps the rendering of the next (mg_step_host) */
 
 struct mg_handle {
