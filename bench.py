@@ -46,7 +46,7 @@ OBS_BYTES_PER_ENV = 96 * 96 * 12       # algorithmic bytes written per env-step 
 # dram__bytes_read.sum + dram__bytes_write.sum of one mg_render_kernel launch at 4096 MoveToCorner envs (ncu --set full);
 # per env it does not depend on the batch size
 NCU_DRAM_BYTES_PER_ENV = (356.310e6 + 537.062e6) / 4096
-NCU_TRAFFIC_SOURCE = 'profiles/r2b_ncu_summary.txt (ncu --set full, one launch, 4096 MoveToCorner envs), scaled per env'
+NCU_TRAFFIC_SOURCE = 'profiles/r2c_ncu_summary.txt (ncu --set full, one launch, 4096 MoveToCorner envs), scaled per env'
 METRIC = 'env_steps_per_sec_lores4e'
 UNIT = 'env-steps/s'
 SCENE_NBLOCKS_WORD = 2                  # int32 index of mg_scene.n_blocks (include/mg_scene.h)
