@@ -695,8 +695,10 @@ extern "C" int mg_debug_read_timers(long long *out_host, int n_ctas)
 /* shape i of the current row, and shape j + manifold of up to NARROW_SLOTS pairs in flight */
 struct NarrowScratch { WShape si; struct { WShape sj; Manifold mf; } slot[NARROW_SLOTS]; };
 
+/* returns the number of live arbiters; bit 8: one of them is on a block's body */
 __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsigned gmask, unsigned char *order, NarrowScratch *scratch, double *bbs, long long *tm = nullptr)
 {
+    int on_block = 0;
     TM_DECL(tm);
     const int gl = lane & (PHYS_LANES - 1);     /* lane within the env's group */
     const double dt = MG_DT;
@@ -809,6 +811,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
                     }
                     __syncwarp(gmask);
                     n_live += order[MG_NARB];
+                    if (body_i >= MG_BODY_BLOCK0 || body_s >= MG_BODY_BLOCK0) on_block = 256;
                 }
                 __syncwarp(gmask);
             }
@@ -827,7 +830,7 @@ __device__ int space_step_parallel(EnvRef e, const MgTables *T, int lane, unsign
         if ((IF(e, I_CON0 + c) & 255) != CON_SPRING) con_prestep(e, c);
     __syncwarp(gmask);
     TM_ADD(TM_P_PRESTEP);
-    return PHYS_DBG_SKIP == 7 ? 0 : n_live;
+    return PHYS_DBG_SKIP == 7 ? 0 : (n_live ? n_live | on_block : 0);
 }
 
 /* ---- the robot's ten constraints with the six robot bodies' velocities in registers.
@@ -1147,8 +1150,10 @@ __device__ __forceinline__ void block_pair_pass(EnvRef e, int c, int b)
  * robot bodies, and every block has one PivotJoint + GearJoint pair to the static body.  So the robot chains of the
  * CTA's envs run side by side in warp 0 (lane k = env k, straight-line register code as before) while each block's pair
  * runs on its own lane of the other warps (lane = (env, block)); every body still sees its own updates in Chipmunk's
- * order.  Contacts can couple any two bodies, so they stay one ordered chain per env on warp 0, fenced from the
- * constraint passes by CTA barriers -- only in CTAs where some env has a live contact (`any_live`, CTA-uniform). */
+ * order.  Contacts can couple any two bodies, so they stay one ordered chain per env on the lead warp, fenced from the
+ * constraint passes by CTA barriers -- only in CTAs where some env has a live contact ON A BLOCK (`any_live`,
+ * CTA-uniform): contacts among the robot's bodies, the walls and nothing else (a robot against a wall, the common case)
+ * touch no body a helper lane touches, so they commute with the blocks' pairs like the robot's constraints do. */
 /* The two roles are separate out-of-line functions so that each gets its own register allocation (the robot chain
  * keeps six bodies' velocities and masses in registers through all ten iterations: inlined into the kernel it spilled
  * inside the constraint pass).  Both pass the same CTA barriers the same number of times (warp-uniform roles). */
@@ -1193,17 +1198,15 @@ __device__ __noinline__ void solve_lead(const bool solver, const int k, const in
     const double gear_inv_ratio = solver ? 1.0 / cf_robot[1 * C_NF + C_P1] : 1.0;     /* GearJoint control -> robot */
     MG_NOUNROLL
     for (int it = 0; it < 10; it++) {               /* space.iterations = phys_iter = 10 */
-        if (any_live) {
-            if (n_live) {
-                /* contacts may involve any body: give them the current velocities and take theirs back */
-                robot_vel_store(es, r);
-                MG_NOUNROLL
-                for (int q = 0; q < n_live; q++) arb_apply_impulse(es, order_s, q);
-                robot_vel_load(es, r);
-            }
-            __syncthreads();
-            TM_ADD(TM_ARB);
+        if (n_live) {
+            /* contacts may involve any body: give them the current velocities and take theirs back */
+            robot_vel_store(es, r);
+            MG_NOUNROLL
+            for (int q = 0; q < n_live; q++) arb_apply_impulse(es, order_s, q);
+            robot_vel_load(es, r);
         }
+        if (any_live) __syncthreads();
+        TM_ADD(TM_ARB);
         if (solver) robot_constraints_pass(r, cf_robot, es.d, gear_inv_ratio);
         TM_ADD(TM_ROBOTCON);
         if (any_live) { __syncthreads(); TM_ADD(TM_BLOCKCON); }
@@ -1663,8 +1666,9 @@ __global__ void __launch_bounds__(PHYS_THREADS_T, 512 / PHYS_THREADS_T) mg_physi
 #else
             int n_live = 0;
 #endif
+            n_live_sub = n_live >> 8;         /* live contacts on a block: the only ones the helper lanes must be fenced from */
+            n_live &= 255;
             if (gl == 0) W->order[MG_NARB + 1] = (unsigned char)n_live;
-            n_live_sub = n_live;
         }
         /* the order-dependent half of the sub-step for all envs of the CTA: robot chains and contacts side by side in
          * warp 0, the blocks' floor-friction pairs on the other warps (solve_lead / solve_helper) */
