@@ -57,7 +57,9 @@
 #define R_STR(x) R_STR2(x)
 #define R_UNROLL(n) _Pragma(R_STR(unroll n))
 #ifndef R_UNROLL_DS
-#define R_UNROLL_DS 1      /* downsample pass 1: quads per lane in flight */
+#define R_UNROLL_DS 3      /* downsample pass 1: quads per thread in flight.  One warp per band (six quads per lane, 96
+                            * registers, 15 warps per SM): 1 was best, every unrolling cost more in code size than it gave.
+                            * Two warps per band: a thread has three quads and all three in flight gain 4 % */
 #endif
 #ifndef R_UNROLL_BG
 #define R_UNROLL_BG 1      /* background clear */
@@ -69,13 +71,15 @@
 #define RENDER_MIN_CTAS (WARPS_PER_BAND == 1 ? 20 : 15)   /* register cap: 96 registers for one warp per band, 64 for two */
 #endif
 #ifndef RENDER_REREAD
-#define RENDER_REREAD 1     /* INPLACE: the stack assembly reads the packed band back instead of keeping it in registers */
+#define RENDER_REREAD 0     /* INPLACE: 1 = the stack assembly reads the packed band back instead of keeping the thread's quads in
+                             * registers (needed at six quads per lane; with three, the registers are there: 2 % faster) */
 #endif
 #ifndef RENDER_INPLACE
 #define RENDER_INPLACE 1    /* fused LoRes4 kernel: downsampled band kept inside the band buffer (see the downsample) */
 #endif
 #ifndef RENDER_PREFETCH
-#define RENDER_PREFETCH 1   /* fetch the next hit's vertices while the current one is painted */
+#define RENDER_PREFETCH 0   /* 1 = fetch the next hit's vertices while the current one is painted: +4 % with one warp per band; with
+                             * two, the partner warp covers that latency and the registers the prefetch holds cost 2 % */
 #endif
 
 struct aff { double a, b, tx, c, d, ty; };   /* 3x3 homogeneous matrix, last row 0 0 1 */
