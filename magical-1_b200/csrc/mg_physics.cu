@@ -1847,7 +1847,11 @@ void mg_launch_physics(const MgDeviceState &S, const int32_t *actions, float *re
      * whatever is left: the largest size that keeps the CTA shape and the number of resident CTAs */
     const size_t smem_sm = 233472, smem_cta_reserved = 1024;
     auto per_env_bytes = [&](int pool) { return (size_t)phys_smem_doubles(max_blocks, pool) * sizeof(double) + sizeof(PhysSmemFixed); };
-    auto is_wide = [&](int pool) { return 2 * (PHYS_TABLE_BYTES + per_env_bytes(pool) * PHYS_ENVS + smem_cta_reserved) <= smem_sm; };
+    static const int force_shape = getenv("MG_PHYS_ENVS_PER_CTA") ? atoi(getenv("MG_PHYS_ENVS_PER_CTA")) : 0;   /* 8 / 16: timing experiments */
+    auto is_wide = [&](int pool) {
+        if (force_shape == PHYS_ENVS / 2) return false;
+        return 2 * (PHYS_TABLE_BYTES + per_env_bytes(pool) * PHYS_ENVS + smem_cta_reserved) <= smem_sm;
+    };
     auto resident = [&](int pool) {
         const int envs_ = is_wide(pool) ? PHYS_ENVS : PHYS_ENVS / 2;
         const int by_smem = (int)(smem_sm / (PHYS_TABLE_BYTES + per_env_bytes(pool) * envs_ + smem_cta_reserved));
