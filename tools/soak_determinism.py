@@ -1,4 +1,6 @@
-"""Dev tool: two handles with the same seed stepped side by side at full batch size (auto-reset on): every observation\nbyte and every body state must agree -- a statistical check for races in the kernels (two warps per rendered band, the\noverlapped step).  usage: python tools/soak_determinism.py"""
+"""Dev tool: two handles with the same seed stepped side by side at full batch size (auto-reset on): every observation
+byte and every body state must agree -- a statistical check for races in the kernels (two warps per rendered band, the
+overlapped step).  usage: python tools/soak_determinism.py"""
 import sys, numpy as np, torch
 sys.path.insert(0, '.')
 import magical_b200 as m
