@@ -15,6 +15,7 @@
 #include "mg_hostasm.h"
 #include <chrono>
 #include <thread>
+#include <sched.h>
 #include "../../include/mg_trig.h"
 
 #define MG_STEP_PARTS 64   /* parts of the batch mg_step runs on their own streams */
@@ -541,7 +542,14 @@ extern "C" int mg_set_host_assembly(mg_handle *h, int mode, int chunks, int n_th
         if (!h->ring_host) CK(h, cudaMallocHost(&h->ring_host, (size_t)h->cfg.num_envs * MG_MAX_RING * MG_FRAME_BYTES));
         if (n_threads <= 0) {
             const char *ev = getenv("MG_HOST_THREADS");
-            n_threads = ev ? atoi(ev) : (int)std::thread::hardware_concurrency();
+            n_threads = ev ? atoi(ev) : 0;
+            if (n_threads <= 0) {
+                /* the CPUs this process may run on (a container's share), not the machine's */
+                cpu_set_t set;
+                CPU_ZERO(&set);
+                if (sched_getaffinity(0, sizeof(set), &set) == 0) n_threads = CPU_COUNT(&set);
+                if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
+            }
             if (n_threads <= 0) n_threads = 1;
             if (n_threads > 64) n_threads = 64;
         }
